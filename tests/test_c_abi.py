@@ -1,0 +1,66 @@
+"""The C-ABI library loads and exports every symbol include/tsb200.h declares (no compute here)."""
+
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from torchsnapshot_b200 import _native
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_in_header():
+    text = open(os.path.join(ROOT, "include", "tsb200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(tsb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_and_binding_agree():
+    assert _declared_in_header() == _native.declared_symbols()
+
+
+def test_library_exports_every_declared_symbol():
+    lib = ctypes.CDLL(_native.LIB_PATH)
+    for name in _declared_in_header():
+        assert hasattr(lib, name), name
+
+
+def test_version_and_struct_layout():
+    lib = _native.load_library()
+    assert lib.tsb_version() == 1000
+    assert _native.REGION_DTYPE.itemsize == 128
+    assert _native.REGION_DTYPE.fields["size"][1] == 32
+    assert _native.REGION_DTYPE.fields["src_stride"][1] == 64
+    assert _native.REGION_DTYPE.fields["dst_stride"][1] == 96
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_context_creation_fails_loudly_without_gpu():
+    with pytest.raises(_native.TsbError):
+        _native.Context(0)
+
+
+def test_missing_library_is_an_error(tmp_path):
+    with pytest.raises(_native.TsbError):
+        _native.load_library(str(tmp_path / "libtsb200.so"))
+
+
+def test_host_helpers(tmp_path):
+    # host-side helpers need no GPU: parallel memcpy and the file fast path
+    import numpy as np
+
+    src = np.random.RandomState(0).randint(0, 256, size=(9 << 20) + 13).astype(np.uint8)
+    dst = np.zeros_like(src)
+    _native.host_memcpy(dst.ctypes.data, src.ctypes.data, src.nbytes, 4)
+    assert np.array_equal(src, dst)
+    path = str(tmp_path / "f.bin")
+    _native.file_write(path, src.ctypes.data, src.nbytes, 4)
+    assert os.path.getsize(path) == src.nbytes
+    back = np.zeros(1 << 20, dtype=np.uint8)
+    _native.file_read(path, 12345, back.ctypes.data, back.nbytes, 2)
+    assert np.array_equal(back, src[12345 : 12345 + (1 << 20)])
+    with pytest.raises(_native.TsbError):
+        _native.file_read(str(tmp_path / "missing"), 0, back.ctypes.data, 16, 1)

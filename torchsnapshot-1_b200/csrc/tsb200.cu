@@ -1,0 +1,789 @@
+// libtsb200.so -- C-ABI implementation (see include/tsb200.h for the contract and the
+// reference call sites each entry point replaces).  CUDA runtime only; no torch types.
+#include <cuda_runtime.h>
+#include <errno.h>
+#include <fcntl.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <map>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "copy_kernel.cuh"
+
+static_assert(sizeof(TsbRegion) == 128, "TsbRegion must be 128 bytes");
+static_assert(sizeof(TsbTile) == 16, "TsbTile must be 16 bytes");
+
+#define TSB_TILE_BYTES (64u * 1024u)
+
+// ------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int set_err(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                             \
+  do {                                                                                             \
+    cudaError_t _e = (expr);                                                                       \
+    if (_e != cudaSuccess)                                                                         \
+      return set_err(TSB_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                     __LINE__);                                                                    \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------
+// arena: segments obtained from the driver on demand, first-fit free lists inside
+// ------------------------------------------------------------------------------------------
+struct Segment {
+  uint64_t base = 0;
+  uint64_t size = 0;
+  std::map<uint64_t, uint64_t> free_blocks;  // offset -> size
+  std::map<uint64_t, uint64_t> used_blocks;  // offset -> size
+};
+
+class Arena {
+ public:
+  Arena(bool host, uint64_t bound, uint64_t seg_default, uint64_t align)
+      : host_(host), bound_(bound), seg_default_(seg_default), align_(align) {}
+
+  int alloc(uint64_t nbytes, uint64_t* out) {
+    if (nbytes == 0) nbytes = 1;
+    const uint64_t need = (nbytes + align_ - 1) / align_ * align_;
+    std::lock_guard<std::mutex> g(mu_);
+    if (try_alloc(need, out)) return TSB_OK;
+    if (need > bound_)
+      return set_err(TSB_ENOMEM, "%s arena: request of %llu bytes exceeds the arena bound of %llu bytes",
+                     host_ ? "host" : "device", (unsigned long long)need, (unsigned long long)bound_);
+    // grow: a new segment if the bound allows it, else drop empty segments first
+    if (reserved_ + need > bound_) release_empty_segments();
+    if (reserved_ + need > bound_) return set_err(TSB_EAGAIN, "%s arena full", host_ ? "host" : "device");
+    uint64_t seg = std::max(need, seg_default_);
+    if (reserved_ + seg > bound_) seg = bound_ - reserved_;
+    uint64_t base = 0;
+    cudaError_t e = raw_alloc(seg, &base);
+    if (e != cudaSuccess && seg > need) {
+      (void)cudaGetLastError();
+      seg = need;
+      e = raw_alloc(seg, &base);
+    }
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      if (in_use_ > 0) return set_err(TSB_EAGAIN, "%s arena: driver allocation failed (%s), retry after a free",
+                                      host_ ? "host" : "device", cudaGetErrorString(e));
+      return set_err(TSB_ENOMEM, "%s arena: driver allocation of %llu bytes failed: %s", host_ ? "host" : "device",
+                     (unsigned long long)seg, cudaGetErrorString(e));
+    }
+    Segment s;
+    s.base = base;
+    s.size = seg;
+    s.free_blocks[0] = seg;
+    segs_.push_back(std::move(s));
+    reserved_ += seg;
+    if (!try_alloc(need, out)) return set_err(TSB_ENOMEM, "arena: internal error");
+    return TSB_OK;
+  }
+
+  int free(uint64_t addr) {
+    std::lock_guard<std::mutex> g(mu_);
+    for (auto& s : segs_) {
+      if (addr < s.base || addr >= s.base + s.size) continue;
+      const uint64_t off = addr - s.base;
+      auto it = s.used_blocks.find(off);
+      if (it == s.used_blocks.end()) break;
+      uint64_t sz = it->second;
+      s.used_blocks.erase(it);
+      in_use_ -= sz;
+      // coalesce with neighbours
+      uint64_t lo = off, hi = off + sz;
+      auto nxt = s.free_blocks.lower_bound(off);
+      if (nxt != s.free_blocks.end() && nxt->first == hi) {
+        hi += nxt->second;
+        nxt = s.free_blocks.erase(nxt);
+      }
+      if (nxt != s.free_blocks.begin()) {
+        auto prv = std::prev(nxt);
+        if (prv->first + prv->second == lo) {
+          lo = prv->first;
+          s.free_blocks.erase(prv);
+        }
+      }
+      s.free_blocks[lo] = hi - lo;
+      return TSB_OK;
+    }
+    return set_err(TSB_EINVAL, "arena: address 0x%llx was not allocated here", (unsigned long long)addr);
+  }
+
+  // segment that contains addr (for IPC export)
+  bool find_segment(uint64_t addr, uint64_t* base, uint64_t* size) {
+    std::lock_guard<std::mutex> g(mu_);
+    for (auto& s : segs_)
+      if (addr >= s.base && addr < s.base + s.size) {
+        *base = s.base;
+        *size = s.size;
+        return true;
+      }
+    return false;
+  }
+
+  void stats(uint64_t* in_use, uint64_t* reserved, uint64_t* bound) {
+    std::lock_guard<std::mutex> g(mu_);
+    *in_use = in_use_;
+    *reserved = reserved_;
+    *bound = bound_;
+  }
+
+  void trim() {
+    std::lock_guard<std::mutex> g(mu_);
+    release_empty_segments();
+  }
+
+  void destroy() {
+    std::lock_guard<std::mutex> g(mu_);
+    for (auto& s : segs_) raw_free(s.base);
+    segs_.clear();
+    reserved_ = in_use_ = 0;
+  }
+
+ private:
+  bool try_alloc(uint64_t need, uint64_t* out) {
+    for (auto& s : segs_) {
+      for (auto it = s.free_blocks.begin(); it != s.free_blocks.end(); ++it) {
+        if (it->second < need) continue;
+        const uint64_t off = it->first, sz = it->second;
+        s.free_blocks.erase(it);
+        if (sz > need) s.free_blocks[off + need] = sz - need;
+        s.used_blocks[off] = need;
+        in_use_ += need;
+        *out = s.base + off;
+        return true;
+      }
+    }
+    return false;
+  }
+  void release_empty_segments() {
+    for (size_t i = 0; i < segs_.size();) {
+      if (segs_[i].used_blocks.empty()) {
+        raw_free(segs_[i].base);
+        reserved_ -= segs_[i].size;
+        segs_.erase(segs_.begin() + i);
+      } else {
+        ++i;
+      }
+    }
+  }
+  cudaError_t raw_alloc(uint64_t n, uint64_t* base) {
+    void* p = nullptr;
+    cudaError_t e = host_ ? cudaHostAlloc(&p, n, cudaHostAllocPortable) : cudaMalloc(&p, n);
+    *base = (uint64_t)(uintptr_t)p;
+    return e;
+  }
+  void raw_free(uint64_t base) {
+    if (host_)
+      cudaFreeHost((void*)(uintptr_t)base);
+    else
+      cudaFree((void*)(uintptr_t)base);
+  }
+
+  bool host_;
+  uint64_t bound_, seg_default_, align_;
+  uint64_t reserved_ = 0, in_use_ = 0;
+  std::vector<Segment> segs_;
+  std::mutex mu_;
+};
+
+// ------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------
+struct PendingScratch {
+  cudaEvent_t done;
+  uint64_t hbuf;
+  uint64_t dbuf;
+};
+
+struct TsbCtx {
+  int device = 0;
+  int sm_count = 0;
+  int ctas_per_sm = TSB_CTAS_PER_SM;
+  cudaStream_t streams[TSB_NUM_STREAMS] = {};
+  Arena* host_arena = nullptr;
+  Arena* dev_arena = nullptr;
+  std::mutex mu;  // events + scratch list
+  std::vector<cudaEvent_t> events;
+  std::vector<uint32_t> event_gen;
+  std::vector<uint32_t> free_events;
+  std::vector<PendingScratch> pending;
+  std::vector<cudaEvent_t> spare_scratch_events;
+};
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+#define CHECK_CTX(ctx)                                     \
+  if ((ctx) == nullptr) return set_err(TSB_EINVAL, "null context"); \
+  DeviceGuard _guard((ctx)->device);                       \
+  if (!_guard.ok) return set_err(TSB_ECUDA, "cudaSetDevice(%d) failed", (ctx)->device)
+
+#define CHECK_STREAM(s) \
+  if ((s) < 0 || (s) >= TSB_NUM_STREAMS) return set_err(TSB_EINVAL, "bad stream index %d", (s))
+
+static int event_lookup(TsbCtx* ctx, TsbEvent h, cudaEvent_t* out) {
+  const uint32_t idx = (uint32_t)(h & 0xffffffffu), gen = (uint32_t)(h >> 32);
+  std::lock_guard<std::mutex> g(ctx->mu);
+  if (idx == 0 || idx > ctx->events.size() || ctx->event_gen[idx - 1] != gen)
+    return set_err(TSB_EINVAL, "stale or invalid event handle 0x%llx", (unsigned long long)h);
+  *out = ctx->events[idx - 1];
+  return TSB_OK;
+}
+
+// free scratch of launches that have completed (caller holds no lock)
+static void reap_scratch(TsbCtx* ctx, bool wait_all) {
+  std::vector<PendingScratch> done;
+  {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    for (size_t i = 0; i < ctx->pending.size();) {
+      cudaError_t q = wait_all ? cudaEventSynchronize(ctx->pending[i].done) : cudaEventQuery(ctx->pending[i].done);
+      if (q == cudaErrorNotReady) {
+        ++i;
+        continue;
+      }
+      if (q != cudaSuccess) (void)cudaGetLastError();
+      done.push_back(ctx->pending[i]);
+      ctx->spare_scratch_events.push_back(ctx->pending[i].done);
+      ctx->pending.erase(ctx->pending.begin() + i);
+    }
+  }
+  for (auto& p : done) {
+    if (p.hbuf) ctx->host_arena->free(p.hbuf);
+    if (p.dbuf) ctx->dev_arena->free(p.dbuf);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// tile table
+// ------------------------------------------------------------------------------------------
+static int validate_region(const TsbRegion& r, uint32_t i) {
+  if (r.ndim > TSB_MAX_DIMS) return set_err(TSB_EINVAL, "region %u: ndim %u > %d", i, r.ndim, TSB_MAX_DIMS);
+  if (r.run_bytes == 0) return TSB_OK;
+  if ((r.src == 0 || r.dst == 0)) return set_err(TSB_EINVAL, "region %u: null address", i);
+  return TSB_OK;
+}
+
+// Payload bytes of a region; false on overflow.
+static bool region_payload(const TsbRegion& r, uint64_t* total) {
+  unsigned __int128 t = r.run_bytes;
+  for (uint32_t d = 0; d < r.ndim; ++d) {
+    t *= r.size[d];
+    if (t >> 63) return false;
+  }
+  *total = (uint64_t)t;
+  return true;
+}
+
+static int build_tiles(const TsbRegion* regions, uint32_t n, std::vector<TsbTile>& tiles) {
+  for (uint32_t i = 0; i < n; ++i) {
+    const TsbRegion& r = regions[i];
+    int rc = validate_region(r, i);
+    if (rc != TSB_OK) return rc;
+    uint64_t total;
+    if (!region_payload(r, &total)) return set_err(TSB_EINVAL, "region %u: size overflow", i);
+    if (total == 0) continue;
+    uint64_t step = TSB_TILE_BYTES;
+    if (r.ndim > 0 && r.run_bytes < TSB_CTA_RUN_MIN) {
+      // warp / element classes: tiles hold whole runs
+      uint64_t runs = TSB_TILE_BYTES / r.run_bytes;
+      if (runs == 0) runs = 1;
+      step = runs * r.run_bytes;
+    }
+    for (uint64_t off = 0; off < total; off += step) {
+      TsbTile t;
+      t.off = off;
+      t.len = (uint32_t)std::min<uint64_t>(step, total - off);
+      t.region = i;
+      tiles.push_back(t);
+    }
+  }
+  return TSB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// C-ABI
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+int tsb_version(void) { return 1000; }
+
+const char* tsb_last_error(void) { return g_err; }
+
+int tsb_device_count(int* count) {
+  if (!count) return set_err(TSB_EINVAL, "null argument");
+  CUDA_TRY(cudaGetDeviceCount(count));
+  return TSB_OK;
+}
+
+int tsb_ctx_create(int device, uint64_t host_arena_max, uint64_t dev_arena_max, TsbCtx** out) {
+  if (!out) return set_err(TSB_EINVAL, "null argument");
+  int count = 0;
+  CUDA_TRY(cudaGetDeviceCount(&count));
+  if (device < 0 || device >= count) return set_err(TSB_EINVAL, "device %d out of range (%d visible)", device, count);
+  DeviceGuard guard(device);
+  if (!guard.ok) return set_err(TSB_ECUDA, "cudaSetDevice(%d) failed", device);
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10)
+    return set_err(TSB_ECUDA, "device %d is sm_%d%d; libtsb200 carries sm_100a code only", device, prop.major,
+                   prop.minor);
+  TsbCtx* ctx = new TsbCtx();
+  ctx->device = device;
+  ctx->sm_count = prop.multiProcessorCount;
+  for (int i = 0; i < TSB_NUM_STREAMS; ++i) {
+    cudaError_t e = cudaStreamCreateWithFlags(&ctx->streams[i], cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+      delete ctx;
+      return set_err(TSB_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e));
+    }
+  }
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tsb_copy_regions_kernel, TSB_THREADS, 0) == cudaSuccess &&
+      occ > 0)
+    ctx->ctas_per_sm = occ;
+  else
+    (void)cudaGetLastError();
+  if (host_arena_max == 0) host_arena_max = 4ull << 30;
+  if (dev_arena_max == 0) dev_arena_max = 16ull << 30;
+  ctx->host_arena = new Arena(true, host_arena_max, 256ull << 20, 4096);
+  ctx->dev_arena = new Arena(false, dev_arena_max, 256ull << 20, 512);
+  *out = ctx;
+  return TSB_OK;
+}
+
+int tsb_ctx_destroy(TsbCtx* ctx) {
+  CHECK_CTX(ctx);
+  for (int i = 0; i < TSB_NUM_STREAMS; ++i) cudaStreamSynchronize(ctx->streams[i]);
+  reap_scratch(ctx, true);
+  for (auto e : ctx->events) cudaEventDestroy(e);
+  for (auto e : ctx->spare_scratch_events) cudaEventDestroy(e);
+  for (int i = 0; i < TSB_NUM_STREAMS; ++i) cudaStreamDestroy(ctx->streams[i]);
+  ctx->host_arena->destroy();
+  ctx->dev_arena->destroy();
+  delete ctx->host_arena;
+  delete ctx->dev_arena;
+  delete ctx;
+  (void)cudaGetLastError();
+  return TSB_OK;
+}
+
+int tsb_ctx_device(TsbCtx* ctx, int* device) {
+  if (!ctx || !device) return set_err(TSB_EINVAL, "null argument");
+  *device = ctx->device;
+  return TSB_OK;
+}
+
+int tsb_ctx_sm_count(TsbCtx* ctx, int* sms) {
+  if (!ctx || !sms) return set_err(TSB_EINVAL, "null argument");
+  *sms = ctx->sm_count;
+  return TSB_OK;
+}
+
+int tsb_dev_alloc(TsbCtx* ctx, uint64_t nbytes, uint64_t* dptr) {
+  CHECK_CTX(ctx);
+  if (!dptr) return set_err(TSB_EINVAL, "null argument");
+  int rc = ctx->dev_arena->alloc(nbytes, dptr);
+  if (rc == TSB_EAGAIN) {
+    reap_scratch(ctx, false);
+    rc = ctx->dev_arena->alloc(nbytes, dptr);
+  }
+  return rc;
+}
+
+int tsb_dev_free(TsbCtx* ctx, uint64_t dptr) {
+  CHECK_CTX(ctx);
+  return ctx->dev_arena->free(dptr);
+}
+
+int tsb_host_alloc(TsbCtx* ctx, uint64_t nbytes, void** hptr) {
+  CHECK_CTX(ctx);
+  if (!hptr) return set_err(TSB_EINVAL, "null argument");
+  uint64_t a = 0;
+  int rc = ctx->host_arena->alloc(nbytes, &a);
+  if (rc == TSB_EAGAIN) {
+    reap_scratch(ctx, false);
+    rc = ctx->host_arena->alloc(nbytes, &a);
+  }
+  *hptr = (void*)(uintptr_t)a;
+  return rc;
+}
+
+int tsb_host_free(TsbCtx* ctx, void* hptr) {
+  CHECK_CTX(ctx);
+  return ctx->host_arena->free((uint64_t)(uintptr_t)hptr);
+}
+
+int tsb_arena_stats(TsbCtx* ctx, int which, uint64_t* in_use, uint64_t* reserved, uint64_t* bound) {
+  if (!ctx || !in_use || !reserved || !bound) return set_err(TSB_EINVAL, "null argument");
+  (which == 0 ? ctx->host_arena : ctx->dev_arena)->stats(in_use, reserved, bound);
+  return TSB_OK;
+}
+
+int tsb_arena_trim(TsbCtx* ctx) {
+  CHECK_CTX(ctx);
+  reap_scratch(ctx, false);
+  ctx->host_arena->trim();
+  ctx->dev_arena->trim();
+  return TSB_OK;
+}
+
+int tsb_event_record(TsbCtx* ctx, int stream, TsbEvent* ev) {
+  CHECK_CTX(ctx);
+  CHECK_STREAM(stream);
+  if (!ev) return set_err(TSB_EINVAL, "null argument");
+  uint32_t idx;
+  cudaEvent_t e = nullptr;
+  {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    if (!ctx->free_events.empty()) {
+      idx = ctx->free_events.back();
+      ctx->free_events.pop_back();
+    } else {
+      cudaEvent_t ne;
+      CUDA_TRY(cudaEventCreate(&ne));
+      ctx->events.push_back(ne);
+      ctx->event_gen.push_back(1);
+      idx = (uint32_t)ctx->events.size();
+    }
+    e = ctx->events[idx - 1];
+    *ev = (uint64_t)idx | ((uint64_t)ctx->event_gen[idx - 1] << 32);
+  }
+  CUDA_TRY(cudaEventRecord(e, ctx->streams[stream]));
+  return TSB_OK;
+}
+
+int tsb_stream_wait_event(TsbCtx* ctx, int stream, TsbEvent ev) {
+  CHECK_CTX(ctx);
+  CHECK_STREAM(stream);
+  cudaEvent_t e = nullptr;
+  int rc = event_lookup(ctx, ev, &e);
+  if (rc != TSB_OK) return rc;
+  CUDA_TRY(cudaStreamWaitEvent(ctx->streams[stream], e, 0));
+  return TSB_OK;
+}
+
+int tsb_event_query(TsbCtx* ctx, TsbEvent ev) {
+  CHECK_CTX(ctx);
+  cudaEvent_t e = nullptr;
+  int rc = event_lookup(ctx, ev, &e);
+  if (rc != TSB_OK) return rc;
+  cudaError_t q = cudaEventQuery(e);
+  if (q == cudaSuccess) return TSB_OK;
+  if (q == cudaErrorNotReady) {
+    (void)cudaGetLastError();
+    return TSB_EAGAIN;
+  }
+  return set_err(TSB_ECUDA, "cudaEventQuery failed: %s", cudaGetErrorString(q));
+}
+
+int tsb_event_sync(TsbCtx* ctx, TsbEvent ev) {
+  CHECK_CTX(ctx);
+  cudaEvent_t e = nullptr;
+  int rc = event_lookup(ctx, ev, &e);
+  if (rc != TSB_OK) return rc;
+  CUDA_TRY(cudaEventSynchronize(e));
+  return TSB_OK;
+}
+
+int tsb_event_elapsed_ms(TsbCtx* ctx, TsbEvent start, TsbEvent stop, float* ms) {
+  CHECK_CTX(ctx);
+  if (!ms) return set_err(TSB_EINVAL, "null argument");
+  cudaEvent_t a = nullptr, b = nullptr;
+  int rc = event_lookup(ctx, start, &a);
+  if (rc != TSB_OK) return rc;
+  rc = event_lookup(ctx, stop, &b);
+  if (rc != TSB_OK) return rc;
+  CUDA_TRY(cudaEventElapsedTime(ms, a, b));
+  return TSB_OK;
+}
+
+int tsb_event_release(TsbCtx* ctx, TsbEvent ev) {
+  if (!ctx) return set_err(TSB_EINVAL, "null context");
+  const uint32_t idx = (uint32_t)(ev & 0xffffffffu), gen = (uint32_t)(ev >> 32);
+  std::lock_guard<std::mutex> g(ctx->mu);
+  if (idx == 0 || idx > ctx->events.size() || ctx->event_gen[idx - 1] != gen)
+    return set_err(TSB_EINVAL, "stale or invalid event handle 0x%llx", (unsigned long long)ev);
+  ctx->event_gen[idx - 1] += 1;
+  if (ctx->event_gen[idx - 1] == 0) ctx->event_gen[idx - 1] = 1;
+  ctx->free_events.push_back(idx);
+  return TSB_OK;
+}
+
+int tsb_stream_wait_external(TsbCtx* ctx, int stream, uint64_t cuda_stream) {
+  CHECK_CTX(ctx);
+  CHECK_STREAM(stream);
+  cudaEvent_t e = nullptr;
+  CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  cudaError_t r = cudaEventRecord(e, (cudaStream_t)(uintptr_t)cuda_stream);
+  if (r == cudaSuccess) r = cudaStreamWaitEvent(ctx->streams[stream], e, 0);
+  cudaEventDestroy(e);  // destruction is deferred by the runtime until the event completes
+  if (r != cudaSuccess) return set_err(TSB_ECUDA, "stream_wait_external failed: %s", cudaGetErrorString(r));
+  return TSB_OK;
+}
+
+int tsb_external_wait_stream(TsbCtx* ctx, uint64_t cuda_stream, int stream) {
+  CHECK_CTX(ctx);
+  CHECK_STREAM(stream);
+  cudaEvent_t e = nullptr;
+  CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  cudaError_t r = cudaEventRecord(e, ctx->streams[stream]);
+  if (r == cudaSuccess) r = cudaStreamWaitEvent((cudaStream_t)(uintptr_t)cuda_stream, e, 0);
+  cudaEventDestroy(e);
+  if (r != cudaSuccess) return set_err(TSB_ECUDA, "external_wait_stream failed: %s", cudaGetErrorString(r));
+  return TSB_OK;
+}
+
+int tsb_stream_sync(TsbCtx* ctx, int stream) {
+  CHECK_CTX(ctx);
+  CHECK_STREAM(stream);
+  CUDA_TRY(cudaStreamSynchronize(ctx->streams[stream]));
+  return TSB_OK;
+}
+
+int tsb_copy_regions(TsbCtx* ctx, int stream, const TsbRegion* regions, uint32_t n) {
+  CHECK_CTX(ctx);
+  CHECK_STREAM(stream);
+  if (n == 0) return TSB_OK;
+  if (!regions) return set_err(TSB_EINVAL, "null regions");
+  reap_scratch(ctx, false);
+  std::vector<TsbTile> tiles;
+  tiles.reserve(n + 1024);
+  int rc = build_tiles(regions, n, tiles);
+  if (rc != TSB_OK) return rc;
+  if (tiles.empty()) return TSB_OK;
+  if (tiles.size() > 0xffffffffull) return set_err(TSB_EINVAL, "too many tiles in one launch");
+  const uint64_t reg_bytes = (uint64_t)n * sizeof(TsbRegion);
+  const uint64_t tile_bytes = (uint64_t)tiles.size() * sizeof(TsbTile);
+  const uint64_t total = reg_bytes + tile_bytes;
+  uint64_t hbuf = 0, dbuf = 0;
+  rc = ctx->host_arena->alloc(total, &hbuf);
+  if (rc != TSB_OK) return rc;
+  rc = ctx->dev_arena->alloc(total, &dbuf);
+  if (rc != TSB_OK) {
+    ctx->host_arena->free(hbuf);
+    return rc;
+  }
+  memcpy((void*)(uintptr_t)hbuf, regions, reg_bytes);
+  memcpy((void*)(uintptr_t)(hbuf + reg_bytes), tiles.data(), tile_bytes);
+  cudaStream_t s = ctx->streams[stream];
+  cudaError_t e = cudaMemcpyAsync((void*)(uintptr_t)dbuf, (void*)(uintptr_t)hbuf, total, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) {
+    const uint32_t n_tiles = (uint32_t)tiles.size();
+    const uint32_t grid = (uint32_t)std::min<uint64_t>(n_tiles, (uint64_t)ctx->sm_count * ctx->ctas_per_sm);
+    tsb_copy_regions_kernel<<<grid, TSB_THREADS, 0, s>>>((const TsbRegion*)(uintptr_t)dbuf,
+                                                         (const TsbTile*)(uintptr_t)(dbuf + reg_bytes), n_tiles);
+    e = cudaGetLastError();
+  }
+  // the scratch is released once the launch has completed
+  PendingScratch p;
+  p.hbuf = hbuf;
+  p.dbuf = dbuf;
+  p.done = nullptr;
+  {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    if (!ctx->spare_scratch_events.empty()) {
+      p.done = ctx->spare_scratch_events.back();
+      ctx->spare_scratch_events.pop_back();
+    }
+  }
+  if (p.done == nullptr && cudaEventCreateWithFlags(&p.done, cudaEventDisableTiming) != cudaSuccess) {
+    cudaStreamSynchronize(s);
+    ctx->host_arena->free(hbuf);
+    ctx->dev_arena->free(dbuf);
+    return set_err(TSB_ECUDA, "cudaEventCreate failed");
+  }
+  cudaEventRecord(p.done, s);
+  {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->pending.push_back(p);
+  }
+  if (e != cudaSuccess) return set_err(TSB_ECUDA, "copy_regions launch failed: %s", cudaGetErrorString(e));
+  return TSB_OK;
+}
+
+int tsb_memcpy_d2h(TsbCtx* ctx, int stream, void* hptr, uint64_t dptr, uint64_t nbytes) {
+  CHECK_CTX(ctx);
+  CHECK_STREAM(stream);
+  if (nbytes == 0) return TSB_OK;
+  CUDA_TRY(cudaMemcpyAsync(hptr, (const void*)(uintptr_t)dptr, nbytes, cudaMemcpyDeviceToHost, ctx->streams[stream]));
+  return TSB_OK;
+}
+
+int tsb_memcpy_h2d(TsbCtx* ctx, int stream, uint64_t dptr, const void* hptr, uint64_t nbytes) {
+  CHECK_CTX(ctx);
+  CHECK_STREAM(stream);
+  if (nbytes == 0) return TSB_OK;
+  CUDA_TRY(cudaMemcpyAsync((void*)(uintptr_t)dptr, hptr, nbytes, cudaMemcpyHostToDevice, ctx->streams[stream]));
+  return TSB_OK;
+}
+
+int tsb_memcpy_d2d(TsbCtx* ctx, int stream, uint64_t dst, uint64_t src, uint64_t nbytes) {
+  CHECK_CTX(ctx);
+  CHECK_STREAM(stream);
+  if (nbytes == 0) return TSB_OK;
+  CUDA_TRY(cudaMemcpyAsync((void*)(uintptr_t)dst, (const void*)(uintptr_t)src, nbytes, cudaMemcpyDefault,
+                           ctx->streams[stream]));
+  return TSB_OK;
+}
+
+// ---- host helpers ---------------------------------------------------------------------------
+static int default_threads(uint64_t nbytes, int nthreads) {
+  if (nthreads <= 0) {
+    unsigned hc = std::thread::hardware_concurrency();
+    nthreads = (int)std::min<unsigned>(hc ? hc : 4, 8);
+  }
+  const uint64_t min_chunk = 4ull << 20;
+  uint64_t by_size = (nbytes + min_chunk - 1) / min_chunk;
+  if (by_size < 1) by_size = 1;
+  return (int)std::min<uint64_t>((uint64_t)nthreads, by_size);
+}
+
+int tsb_host_memcpy(void* dst, const void* src, uint64_t nbytes, int nthreads) {
+  if (nbytes == 0) return TSB_OK;
+  if (!dst || !src) return set_err(TSB_EINVAL, "null argument");
+  const int nt = default_threads(nbytes, nthreads);
+  if (nt <= 1) {
+    memcpy(dst, src, nbytes);
+    return TSB_OK;
+  }
+  std::vector<std::thread> th;
+  const uint64_t chunk = ((nbytes + nt - 1) / nt + 4095) / 4096 * 4096;
+  for (int i = 0; i < nt; ++i) {
+    const uint64_t lo = (uint64_t)i * chunk;
+    if (lo >= nbytes) break;
+    const uint64_t len = std::min(chunk, nbytes - lo);
+    th.emplace_back([=] { memcpy((char*)dst + lo, (const char*)src + lo, len); });
+  }
+  for (auto& t : th) t.join();
+  return TSB_OK;
+}
+
+static int rw_range(int fd, bool write, char* buf, uint64_t off, uint64_t len) {
+  while (len) {
+    ssize_t k = write ? pwrite(fd, buf, len, (off_t)off) : pread(fd, buf, len, (off_t)off);
+    if (k < 0) {
+      if (errno == EINTR) continue;
+      return errno;
+    }
+    if (k == 0) return write ? EIO : ENODATA;
+    buf += k;
+    off += (uint64_t)k;
+    len -= (uint64_t)k;
+  }
+  return 0;
+}
+
+static int file_rw(const char* path, bool write, uint64_t offset, void* hptr, uint64_t nbytes, int nthreads) {
+  if (!path) return set_err(TSB_EINVAL, "null path");
+  int fd = write ? open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644) : open(path, O_RDONLY);
+  if (fd < 0) return set_err(TSB_EIO, "open(%s) failed: %s", path, strerror(errno));
+  int err = 0;
+  if (nbytes) {
+    const int nt = default_threads(nbytes, nthreads);
+    if (nt <= 1) {
+      err = rw_range(fd, write, (char*)hptr, offset, nbytes);
+    } else {
+      std::vector<std::thread> th;
+      std::vector<int> errs(nt, 0);
+      const uint64_t chunk = ((nbytes + nt - 1) / nt + 4095) / 4096 * 4096;
+      for (int i = 0; i < nt; ++i) {
+        const uint64_t lo = (uint64_t)i * chunk;
+        if (lo >= nbytes) break;
+        const uint64_t len = std::min(chunk, nbytes - lo);
+        int* e = &errs[i];
+        th.emplace_back([=] { *e = rw_range(fd, write, (char*)hptr + lo, offset + lo, len); });
+      }
+      for (auto& t : th) t.join();
+      for (int e : errs)
+        if (e) err = e;
+    }
+  }
+  if (close(fd) != 0 && !err) err = errno;
+  if (err) return set_err(TSB_EIO, "%s(%s) failed: %s", write ? "write" : "read", path, strerror(err));
+  return TSB_OK;
+}
+
+int tsb_file_write(const char* path, const void* hptr, uint64_t nbytes, int nthreads) {
+  return file_rw(path, true, 0, const_cast<void*>(hptr), nbytes, nthreads);
+}
+
+int tsb_file_read(const char* path, uint64_t offset, void* hptr, uint64_t nbytes, int nthreads) {
+  return file_rw(path, false, offset, hptr, nbytes, nthreads);
+}
+
+// ---- peer access ------------------------------------------------------------------------------
+int tsb_ipc_export(TsbCtx* ctx, uint64_t dptr, uint8_t* handle, uint64_t* offset) {
+  CHECK_CTX(ctx);
+  if (!handle || !offset) return set_err(TSB_EINVAL, "null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == TSB_IPC_HANDLE_BYTES, "ipc handle size");
+  uint64_t base = 0, size = 0;
+  if (!ctx->dev_arena->find_segment(dptr, &base, &size))
+    return set_err(TSB_EINVAL, "ipc_export: 0x%llx is not device-arena memory", (unsigned long long)dptr);
+  cudaIpcMemHandle_t h;
+  CUDA_TRY(cudaIpcGetMemHandle(&h, (void*)(uintptr_t)base));
+  memcpy(handle, &h, sizeof(h));
+  *offset = dptr - base;
+  return TSB_OK;
+}
+
+int tsb_ipc_open(TsbCtx* ctx, const uint8_t* handle, uint64_t* base) {
+  CHECK_CTX(ctx);
+  if (!handle || !base) return set_err(TSB_EINVAL, "null argument");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  void* p = nullptr;
+  CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *base = (uint64_t)(uintptr_t)p;
+  return TSB_OK;
+}
+
+int tsb_ipc_close(TsbCtx* ctx, uint64_t base) {
+  CHECK_CTX(ctx);
+  CUDA_TRY(cudaIpcCloseMemHandle((void*)(uintptr_t)base));
+  return TSB_OK;
+}
+
+int tsb_peer_enable(TsbCtx* ctx, int peer_device) {
+  CHECK_CTX(ctx);
+  if (peer_device == ctx->device) return TSB_OK;
+  int can = 0;
+  CUDA_TRY(cudaDeviceCanAccessPeer(&can, ctx->device, peer_device));
+  if (!can) return set_err(TSB_ECUDA, "device %d cannot access peer %d", ctx->device, peer_device);
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) {
+    (void)cudaGetLastError();
+    return TSB_OK;
+  }
+  if (e != cudaSuccess) return set_err(TSB_ECUDA, "cudaDeviceEnablePeerAccess failed: %s", cudaGetErrorString(e));
+  return TSB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,243 @@
+"""Manifest entries and the `.snapshot_metadata` document.
+
+The on-disk format is the reference's and is not changed by this build: a JSON document
+(json is a yaml subset) `{"version", "world_size", "manifest": {path: entry}}` where every entry
+is a tagged union keyed by "type" (reference torchsnapshot/manifest.py:28-314).  Only the
+vocabulary is restated here; the field names and their order in the serialised form are what the
+reference writes, so either implementation loads the other's snapshots.
+"""
+
+import base64
+import json
+import struct
+from dataclasses import dataclass, field, fields
+from typing import Any, Dict, List, Optional, Tuple, Union
+
+
+@dataclass
+class Entry:
+    type: str = field(init=False)
+
+    def to_obj(self) -> Dict[str, Any]:
+        return {f.name: _to_obj(getattr(self, f.name)) for f in fields(self)}
+
+
+def _to_obj(v: Any) -> Any:
+    if isinstance(v, (Entry, Shard)):
+        return v.to_obj()
+    if isinstance(v, list):
+        return [_to_obj(x) for x in v]
+    return v
+
+
+@dataclass
+class TensorEntry(Entry):
+    location: str
+    serializer: str
+    dtype: str
+    shape: List[int]
+    replicated: bool
+    byte_range: Optional[List[int]] = None
+
+    def __post_init__(self) -> None:
+        self.type = "Tensor"
+
+    @property
+    def byte_range_tuple(self) -> Optional[Tuple[int, int]]:
+        br = self.byte_range
+        return None if br is None else (br[0], br[1])
+
+
+@dataclass
+class Shard:
+    offsets: List[int]
+    sizes: List[int]
+    tensor: TensorEntry
+
+    def to_obj(self) -> Dict[str, Any]:
+        return {"offsets": list(self.offsets), "sizes": list(self.sizes), "tensor": self.tensor.to_obj()}
+
+
+@dataclass
+class ShardedTensorEntry(Entry):
+    shards: List[Shard]
+
+    def __post_init__(self) -> None:
+        self.type = "ShardedTensor"
+
+
+@dataclass
+class ChunkedTensorEntry(Entry):
+    dtype: str
+    shape: List[int]
+    chunks: List[Shard]
+    replicated: bool
+
+    def __post_init__(self) -> None:
+        self.type = "ChunkedTensor"
+
+
+@dataclass
+class ObjectEntry(Entry):
+    location: str
+    serializer: str
+    obj_type: str
+    replicated: bool
+
+    def __post_init__(self) -> None:
+        self.type = "object"
+
+
+@dataclass
+class ListEntry(Entry):
+    def __post_init__(self) -> None:
+        self.type = "list"
+
+
+@dataclass
+class DictEntry(Entry):
+    keys: List[Union[str, int]]
+
+    def __post_init__(self) -> None:
+        self.type = "dict"
+
+
+@dataclass
+class OrderedDictEntry(Entry):
+    keys: List[Union[str, int]]
+
+    def __post_init__(self) -> None:
+        self.type = "OrderedDict"
+
+
+_PRIMITIVE_TYPES = ("int", "str", "bool", "bytes", "float")
+
+
+@dataclass
+class PrimitiveEntry(Entry):
+    """int/str/bool/bytes/float stored inline in the metadata (reference manifest.py:186-270)."""
+
+    serialized_value: str
+    replicated: bool
+    readable: Optional[str] = None
+    type_name: str = field(default="int", repr=False)
+
+    supported_types = list(_PRIMITIVE_TYPES)
+
+    def __post_init__(self) -> None:
+        self.type = self.type_name
+
+    def to_obj(self) -> Dict[str, Any]:
+        return {
+            "type": self.type,
+            "serialized_value": self.serialized_value,
+            "replicated": self.replicated,
+            "readable": self.readable,
+        }
+
+    def get_value(self) -> Union[int, str, bool, bytes, float]:
+        t, s = self.type, self.serialized_value
+        if t == "int":
+            return int(s)
+        if t == "str":
+            return s
+        if t == "bool":
+            if s not in ("True", "False"):
+                raise RuntimeError(f"Unexpected serialized_value for bool type: {s}")
+            return s == "True"
+        if t == "bytes":
+            return base64.b64decode(s.encode("utf-8"))
+        if t == "float":
+            return struct.unpack("d", base64.b64decode(s.encode("utf-8")))[0]
+        raise ValueError(f"Unable to get deserialized value for {s}")
+
+    @classmethod
+    def from_object(cls, obj: Any) -> "PrimitiveEntry":
+        t = type(obj).__name__
+        if t not in _PRIMITIVE_TYPES:
+            raise TypeError(f"Unsupported primitive obj of type {t}")
+        if t == "bytes":
+            s = base64.b64encode(obj).decode("utf-8")
+        elif t == "float":
+            s = base64.b64encode(struct.pack("d", float(obj))).decode("utf-8")
+        else:
+            s = str(obj)
+        return cls(serialized_value=s, replicated=False, readable=str(obj) if t == "float" else None, type_name=t)
+
+
+Manifest = Dict[str, Entry]
+
+
+def _tensor_from_obj(o: Dict[str, Any]) -> TensorEntry:
+    return TensorEntry(
+        location=o["location"],
+        serializer=o["serializer"],
+        dtype=o["dtype"],
+        shape=list(o["shape"]),
+        replicated=o["replicated"],
+        byte_range=o.get("byte_range"),
+    )
+
+
+def _shard_from_obj(o: Dict[str, Any]) -> Shard:
+    return Shard(offsets=list(o["offsets"]), sizes=list(o["sizes"]), tensor=_tensor_from_obj(o["tensor"]))
+
+
+def entry_from_obj(o: Dict[str, Any]) -> Entry:
+    t = o["type"]
+    if t == "Tensor":
+        return _tensor_from_obj(o)
+    if t == "ShardedTensor":
+        return ShardedTensorEntry(shards=[_shard_from_obj(s) for s in o["shards"]])
+    if t == "ChunkedTensor":
+        return ChunkedTensorEntry(
+            dtype=o["dtype"], shape=list(o["shape"]), chunks=[_shard_from_obj(s) for s in o["chunks"]],
+            replicated=o["replicated"],
+        )
+    if t == "object":
+        return ObjectEntry(location=o["location"], serializer=o["serializer"], obj_type=o["obj_type"],
+                           replicated=o["replicated"])
+    if t == "list":
+        return ListEntry()
+    if t == "dict":
+        return DictEntry(keys=list(o["keys"]))
+    if t == "OrderedDict":
+        return OrderedDictEntry(keys=list(o["keys"]))
+    if t in _PRIMITIVE_TYPES:
+        return PrimitiveEntry(serialized_value=o["serialized_value"], replicated=o["replicated"],
+                              readable=o.get("readable"), type_name=t)
+    raise ValueError(f"Unsupported entry type: {t}")
+
+
+@dataclass
+class SnapshotMetadata:
+    version: str
+    world_size: int
+    manifest: Manifest
+
+    def to_yaml(self) -> str:
+        doc = {
+            "version": self.version,
+            "world_size": self.world_size,
+            "manifest": {path: entry.to_obj() for path, entry in self.manifest.items()},
+        }
+        return json.dumps(doc, sort_keys=False, indent=2)
+
+    @classmethod
+    def from_yaml(cls, text: str) -> "SnapshotMetadata":
+        try:
+            doc = json.loads(text)
+        except json.JSONDecodeError:
+            import yaml  # legacy snapshots written as real yaml
+
+            doc = yaml.safe_load(text)
+        manifest = {path: entry_from_obj(o) for path, o in doc["manifest"].items()}
+        return cls(version=doc["version"], world_size=doc["world_size"], manifest=manifest)
+
+
+def is_container_entry(entry: Any) -> bool:
+    return getattr(entry, "type", None) in ("list", "dict", "OrderedDict")
+
+
+def is_replicated(entry: Any) -> bool:
+    return bool(getattr(entry, "replicated", False))

@@ -1,0 +1,581 @@
+"""Execution of write / read requests: device staging, pinned host ring, overlapped storage I/O.
+
+Entry points keep the reference's names and signatures (torchsnapshot/scheduler.py:220-461):
+`execute_write_reqs` returns a `PendingIOWork` as soon as every request is *staged* (a consistent
+copy exists), `execute_read_reqs` returns when every destination tensor is filled.
+
+What is different underneath:
+
+* take -- all device-stageable requests of a rank (GPU slabs and large CUDA tensors) are packed
+  into ONE device staging block by ONE gather-pack launch per wave; "staged" therefore means
+  "packed in HBM", which costs a few milliseconds, not "copied to host" (the reference blocks the
+  event loop on a pageable .cpu() per slab, batcher.py:141-156).  Each file's bytes then move to a
+  pinned host buffer with one cudaMemcpyAsync on a dedicated copy stream and are handed to
+  StoragePlugin.write as a memoryview while the next copy is already in flight.
+* restore -- each read lands in pinned memory (directly, when the plugin offers `read_into`),
+  crosses PCIe in one H2D copy, and is scattered into the destination tensors by ONE unpack launch
+  per read request (the reference does one pageable H2D copy per tensor in a 4-thread pool,
+  tensor.py:329-338).
+* requests that cannot be staged on the device (CPU tensors, pickled objects, torch_save dtypes,
+  user prepare funcs) go through their own stage_buffer / consume_buffer under the same memory
+  budget rule as the reference.
+"""
+
+import asyncio
+import logging
+import os
+import socket
+import time
+from collections import defaultdict
+from concurrent.futures import Executor, ThreadPoolExecutor
+from typing import Any, Dict, List, Optional, Set, Tuple
+
+import psutil
+
+from . import _native
+from ._native import ArenaFull, STREAM_D2H, STREAM_H2D, STREAM_PACK
+from .engine import Engine, PinnedBuffer, get_engine, readonly_buffer_address
+from .io_types import BufferType, ReadIO, ReadReq, StoragePlugin, WriteIO, WriteReq
+
+logger: logging.Logger = logging.getLogger(__name__)
+
+_MAX_PER_RANK_MEMORY_BUDGET_BYTES: int = 32 * 1024 * 1024 * 1024
+_AVAILABLE_MEMORY_MULTIPLIER: float = 0.6
+_MAX_PER_RANK_CPU_CONCURRENCY: int = 4
+_MAX_PER_RANK_IO_CONCURRENCY: int = 16
+_STAGING_ALIGN = 512  # each file's bytes start 512-B aligned inside the device staging block
+
+
+def get_local_world_size(pg: Any) -> int:
+    hostname = socket.gethostname()
+    obj_list = [None] * pg.get_world_size()
+    pg.all_gather_object(obj_list=obj_list, obj=hostname)
+    return sum(1 for h in obj_list if h == hostname)
+
+
+def get_process_memory_budget_bytes(pg: Any = None) -> int:
+    """Same rule as the reference (scheduler.py:45-65): env override, else
+    min(0.6 * available / local_world_size, 32 GiB)."""
+    if "TORCHSNAPSHOT_PER_RANK_MEMORY_BUDGET_BYTES" in os.environ:
+        try:
+            return int(os.environ["TORCHSNAPSHOT_PER_RANK_MEMORY_BUDGET_BYTES"])
+        except Exception as e:
+            logger.warning(f"Failed to override memory budget: {e}.")
+    available = int(psutil.virtual_memory().available * _AVAILABLE_MEMORY_MULTIPLIER)
+    local_world_size = get_local_world_size(pg) if pg is not None and pg.get_world_size() > 1 else 1
+    return min(available // local_world_size, _MAX_PER_RANK_MEMORY_BUDGET_BYTES)
+
+
+def _is_device_stageable(stager: Any) -> bool:
+    fn = getattr(stager, "is_device_stageable", None)
+    return bool(fn()) if fn is not None else False
+
+
+def _is_device_consumable(consumer: Any) -> bool:
+    fn = getattr(consumer, "is_device_consumable", None)
+    return bool(fn()) if fn is not None else False
+
+
+def _stager_device(stager: Any) -> int:
+    if hasattr(stager, "device"):
+        return int(stager.device)
+    return stager.tensor.device.index or 0
+
+
+def _consumer_device(consumer: Any) -> int:
+    from .batcher import _consumer_device as f
+
+    return f(consumer)
+
+
+def _align(n: int, a: int = _STAGING_ALIGN) -> int:
+    return (n + a - 1) // a * a
+
+
+class _Stats:
+    def __init__(self) -> None:
+        self.begin = time.monotonic()
+        self.bytes = 0
+        self.staging_done: Optional[float] = None
+        # device-timed bracket of the take: first pack launch -> last D2H complete
+        self.pack_events: List[Tuple[Engine, int, int, int]] = []  # (engine, start, stop, kernel bytes)
+        self.d2h_end_events: List[Tuple[Engine, int]] = []
+
+    def pack_ms(self) -> float:
+        """Device time of the pack launches (CUDA events on the pack stream)."""
+        return sum(eng.ctx.event_elapsed_ms(a, b) for eng, a, b, _n in self.pack_events)
+
+    def pack_kernel_bytes(self) -> int:
+        return sum(n for _e, _a, _b, n in self.pack_events)
+
+    def device_ms(self) -> float:
+        """First pack launch -> last D2H complete, per device, max over devices."""
+        worst = 0.0
+        for eng, start, _stop, _n in self.pack_events[:1]:
+            for eng2, end in self.d2h_end_events:
+                if eng2 is eng:
+                    worst = max(worst, eng.ctx.event_elapsed_ms(start, end))
+        return worst
+
+    def release(self) -> None:
+        for eng, a, b, _n in self.pack_events:
+            eng.ctx.event_release(a)
+            eng.ctx.event_release(b)
+        for eng, e in self.d2h_end_events:
+            eng.ctx.event_release(e)
+        self.pack_events = []
+        self.d2h_end_events = []
+
+
+last_write_stats: Optional[_Stats] = None  # introspection hook for bench.py
+
+
+async def _wait_event(loop: asyncio.AbstractEventLoop, executor: Optional[Executor], eng: Engine, ev: int) -> None:
+    await loop.run_in_executor(executor, eng.ctx.event_sync, ev)
+
+
+class _Allocator:
+    """Arena allocation that waits (asynchronously) for a release instead of failing."""
+
+    def __init__(self) -> None:
+        self.released = asyncio.Event()
+        self.outstanding = 0  # allocations handed out through this object and not yet released
+
+    def notify(self) -> None:
+        self.outstanding -= 1
+        self.released.set()
+
+    async def pinned(self, eng: Engine, nbytes: int) -> PinnedBuffer:
+        while True:
+            try:
+                buf = eng.pinned(nbytes)
+                self.outstanding += 1
+                return buf
+            except ArenaFull:
+                await self._wait(eng, "pinned host")
+
+    async def device(self, eng: Engine, nbytes: int) -> int:
+        while True:
+            try:
+                ptr = eng.ctx.dev_alloc(max(nbytes, 1))
+                self.outstanding += 1
+                return ptr
+            except ArenaFull:
+                await self._wait(eng, "device staging")
+
+    async def _wait(self, eng: Engine, what: str) -> None:
+        if self.outstanding == 0:
+            # nothing of ours will ever be released: another take/restore holds the arena
+            await asyncio.sleep(0.002)
+            return
+        self.released.clear()
+        try:
+            await asyncio.wait_for(self.released.wait(), timeout=0.05)
+        except asyncio.TimeoutError:
+            pass
+
+
+# ------------------------------------------------------------------------------------------------
+# write side
+# ------------------------------------------------------------------------------------------------
+class PendingIOWork:
+    """Work left after staging: D2H copies of staged device blocks and storage writes
+    (reference scheduler.py:178-217)."""
+
+    def __init__(self, tasks: Set["asyncio.Future[Any]"], executor: ThreadPoolExecutor, stats: _Stats, rank: int) -> None:
+        self.tasks = tasks
+        self.executor = executor
+        self.stats = stats
+        self.rank = rank
+
+    async def complete(self) -> None:
+        try:
+            while self.tasks:
+                done, _ = await asyncio.wait(self.tasks, return_when=asyncio.FIRST_COMPLETED)
+                for d in done:
+                    self.tasks.discard(d)
+                    d.result()  # surface the first failure
+        except BaseException:
+            for t in self.tasks:
+                t.cancel()
+            await asyncio.gather(*self.tasks, return_exceptions=True)
+            self.tasks.clear()
+            raise
+        finally:
+            self.executor.shutdown(wait=False)
+        elapsed = max(time.monotonic() - self.stats.begin, 1e-9)
+        logger.info(
+            f"Rank {self.rank} completed writing in {elapsed:.3f} s "
+            f"({self.stats.bytes / 1024**2 / elapsed:.1f} MB/s)"
+        )
+
+    def sync_complete(self, event_loop: asyncio.AbstractEventLoop) -> None:
+        event_loop.run_until_complete(self.complete())
+
+
+async def execute_write_reqs(
+    write_reqs: List[WriteReq],
+    storage: StoragePlugin,
+    memory_budget_bytes: int,
+    rank: int,
+) -> PendingIOWork:
+    global last_write_stats
+    loop = asyncio.get_running_loop()
+    executor = ThreadPoolExecutor(max_workers=_MAX_PER_RANK_CPU_CONCURRENCY, thread_name_prefix="tsb-stage")
+    if last_write_stats is not None:
+        try:
+            last_write_stats.release()
+        except Exception:
+            pass
+    stats = _Stats()
+    last_write_stats = stats
+    tasks: Set["asyncio.Future[Any]"] = set()
+    io_slots = asyncio.Semaphore(_MAX_PER_RANK_IO_CONCURRENCY)
+    alloc = _Allocator()
+
+    device_reqs: Dict[int, List[WriteReq]] = defaultdict(list)
+    host_reqs: List[WriteReq] = []
+    for wr in write_reqs:
+        if _is_device_stageable(wr.buffer_stager):
+            device_reqs[_stager_device(wr.buffer_stager)].append(wr)
+        else:
+            host_reqs.append(wr)
+
+    def spawn(coro: Any) -> "asyncio.Future[Any]":
+        t = asyncio.ensure_future(coro)
+        tasks.add(t)
+        return t
+
+    async def write_out(path: str, buf: BufferType, on_done: Any = None) -> None:
+        try:
+            async with io_slots:
+                await storage.write(WriteIO(path=path, buf=buf))
+            stats.bytes += len(buf)
+        finally:
+            if isinstance(buf, memoryview):
+                try:
+                    buf.release()
+                except BufferError:
+                    pass
+            del buf
+            if on_done is not None:
+                on_done()
+
+    async def finish_file(eng: Engine, ev: int, pbuf: PinnedBuffer, path: str) -> None:
+        try:
+            await _wait_event(loop, executor, eng, ev)
+        finally:
+            eng.ctx.event_release(ev)
+        view = pbuf.view()
+        del pbuf
+        await write_out(path, view, alloc.notify)
+
+    async def drain_wave(eng: Engine, base: int, files: List[Tuple[str, int, int]], ev_pack: int) -> None:
+        """D2H of every file of a packed wave, then release of the wave's staging block."""
+        ctx = eng.ctx
+        try:
+            ctx.stream_wait_event(STREAM_D2H, ev_pack)
+            for path, off, nbytes in files:
+                pbuf = await alloc.pinned(eng, nbytes)
+                ctx.memcpy_d2h(STREAM_D2H, pbuf.ptr, base + off, nbytes)
+                ev = ctx.event_record(STREAM_D2H)
+                spawn(finish_file(eng, ev, pbuf, path))
+                del pbuf
+            last_ev = ctx.event_record(STREAM_D2H)
+            await _wait_event(loop, executor, eng, last_ev)
+            stats.d2h_end_events.append((eng, last_ev))
+        finally:
+            ctx.dev_free(base)
+            alloc.notify()
+
+    # ---- 1. device staging: one pack launch per wave -------------------------------------------
+    pack_waits: List[Tuple[Engine, int]] = []
+    for device, reqs in device_reqs.items():
+        eng = get_engine(device)
+        ctx = eng.ctx
+        capacity = max(eng.dev_bound - (64 << 20), 1 << 20)  # leave room for descriptor scratch
+        i = 0
+        first = True
+        while i < len(reqs):
+            # greedy wave: as many requests as the staging bound holds (always at least one)
+            files: List[Tuple[str, int, int]] = []
+            wave_reqs: List[WriteReq] = []
+            total = 0
+            while i < len(reqs):
+                n = reqs[i].buffer_stager.staged_nbytes()
+                if wave_reqs and total + _align(n) > capacity:
+                    break
+                files.append((reqs[i].path, total, n))
+                wave_reqs.append(reqs[i])
+                total += _align(n)
+                i += 1
+            base = await alloc.device(eng, total)
+            regions = []
+            for wr, (_p, off, _n) in zip(wave_reqs, files):
+                regions += wr.buffer_stager.pack_regions(base + off)
+            if first:
+                eng.wait_current_stream(STREAM_PACK)
+                first = False
+            ev_start = ctx.event_record(STREAM_PACK)
+            eng.copy_regions(regions, STREAM_PACK)
+            ev_pack = ctx.event_record(STREAM_PACK)
+            stats.pack_events.append((eng, ev_start, ev_pack, 2 * sum(n for _p, _o, n in files)))
+            pack_waits.append((eng, ev_pack))
+            spawn(drain_wave(eng, base, files, ev_pack))
+            # give the drain a chance to queue its D2H copies before the next wave is planned
+            await asyncio.sleep(0)
+
+    # ---- 2. host staging under the memory budget (reference scheduler.py:255-329) --------------
+    budget = memory_budget_bytes
+    budget_freed = asyncio.Event()
+    inflight_host = 0
+
+    def refund(n: int) -> Any:
+        def cb() -> None:
+            nonlocal budget, inflight_host
+            budget += n
+            inflight_host -= 1
+            budget_freed.set()
+
+        return cb
+
+    for wr in host_reqs:
+        cost = wr.buffer_stager.get_staging_cost_bytes()
+        while inflight_host > 0 and cost >= budget:
+            budget_freed.clear()
+            await budget_freed.wait()
+        budget -= cost
+        inflight_host += 1
+        buf = await wr.buffer_stager.stage_buffer(executor)
+        # the staging cost can exceed the buffer size (2x for torch_save)
+        budget += cost - len(buf)
+        spawn(write_out(wr.path, buf, refund(len(buf))))
+        del buf
+
+    # ---- 3. the snapshot is consistent once every pack launch has completed ---------------------
+    for eng, ev in pack_waits:
+        await _wait_event(loop, executor, eng, ev)
+    stats.staging_done = time.monotonic()
+    logger.info(f"Rank {rank} completed staging in {stats.staging_done - stats.begin:.3f} s")
+    return PendingIOWork(tasks=tasks, executor=executor, stats=stats, rank=rank)
+
+
+def sync_execute_write_reqs(
+    write_reqs: List[WriteReq],
+    storage: StoragePlugin,
+    memory_budget_bytes: int,
+    rank: int,
+    event_loop: asyncio.AbstractEventLoop,
+) -> PendingIOWork:
+    return event_loop.run_until_complete(
+        execute_write_reqs(write_reqs=write_reqs, storage=storage, memory_budget_bytes=memory_budget_bytes, rank=rank)
+    )
+
+
+# ------------------------------------------------------------------------------------------------
+# read side
+# ------------------------------------------------------------------------------------------------
+async def _read_into_pinned(
+    loop: asyncio.AbstractEventLoop,
+    executor: Optional[Executor],
+    storage: StoragePlugin,
+    rr: ReadReq,
+    pbuf: PinnedBuffer,
+    nbytes: int,
+) -> None:
+    read_into = getattr(storage, "read_into", None)
+    if read_into is not None:
+        # plugin fast path: bytes go from the file straight into pinned memory
+        await read_into(rr.path, rr.byte_range, pbuf.view())
+        return
+    read_io = ReadIO(path=rr.path, byte_range=rr.byte_range)
+    await storage.read(read_io=read_io)
+    src = read_io.buf.getbuffer()
+    if len(src) != nbytes:
+        raise AssertionError(f"{rr.path}: expected {nbytes} bytes, the storage plugin returned {len(src)}.")
+    await loop.run_in_executor(executor, _native.host_memcpy, pbuf.ptr, readonly_buffer_address(src), nbytes, 0)
+
+
+async def execute_read_reqs(
+    read_reqs: List[ReadReq],
+    storage: StoragePlugin,
+    memory_budget_bytes: int,
+    rank: int,
+) -> None:
+    loop = asyncio.get_running_loop()
+    executor = ThreadPoolExecutor(max_workers=_MAX_PER_RANK_CPU_CONCURRENCY, thread_name_prefix="tsb-consume")
+    io_slots = asyncio.Semaphore(_MAX_PER_RANK_IO_CONCURRENCY)
+    alloc = _Allocator()
+    begin = time.monotonic()
+    bytes_read = 0
+    ordered: Set[int] = set()
+
+    async def device_read(rr: ReadReq) -> None:
+        nonlocal bytes_read
+        consumer = rr.buffer_consumer
+        eng = get_engine(_consumer_device(consumer))
+        ctx = eng.ctx
+        if eng.device not in ordered:
+            eng.wait_current_stream(STREAM_PACK)  # destination tensors may still be being written
+            ordered.add(eng.device)
+        nbytes = rr.byte_range[1] - rr.byte_range[0] if rr.byte_range is not None else consumer.consumed_nbytes()
+        if nbytes == 0:
+            return
+        async with io_slots:
+            pbuf = await alloc.pinned(eng, nbytes)
+            try:
+                await _read_into_pinned(loop, executor, storage, rr, pbuf, nbytes)
+                dptr = await alloc.device(eng, nbytes)
+                try:
+                    ctx.memcpy_h2d(STREAM_H2D, dptr, pbuf.ptr, nbytes)
+                    ev_h2d = ctx.event_record(STREAM_H2D)
+                    ctx.stream_wait_event(STREAM_PACK, ev_h2d)
+                    ctx.event_release(ev_h2d)
+                    eng.copy_regions(consumer.unpack_regions(dptr), STREAM_PACK)
+                    ev = ctx.event_record(STREAM_PACK)
+                    try:
+                        await _wait_event(loop, executor, eng, ev)
+                    finally:
+                        ctx.event_release(ev)
+                finally:
+                    ctx.dev_free(dptr)
+                    alloc.notify()
+            finally:
+                pbuf.release()
+                alloc.notify()
+        bytes_read += nbytes
+
+    budget = memory_budget_bytes
+    budget_freed = asyncio.Event()
+    inflight_host = 0
+
+    async def host_read(rr: ReadReq, cost: int) -> None:
+        nonlocal bytes_read, budget, inflight_host
+        try:
+            async with io_slots:
+                read_io = ReadIO(path=rr.path, byte_range=rr.byte_range)
+                await storage.read(read_io=read_io)
+                buf = read_io.buf.getvalue()
+            await rr.buffer_consumer.consume_buffer(buf, executor)
+            bytes_read += len(buf)
+        finally:
+            budget += cost
+            inflight_host -= 1
+            budget_freed.set()
+
+    tasks: Set["asyncio.Future[Any]"] = set()
+    try:
+        for rr in read_reqs:
+            if _is_device_consumable(rr.buffer_consumer):
+                tasks.add(asyncio.ensure_future(device_read(rr)))
+                continue
+            cost = rr.buffer_consumer.get_consuming_cost_bytes()
+            while inflight_host > 0 and cost >= budget:
+                budget_freed.clear()
+                await budget_freed.wait()
+            budget -= cost
+            inflight_host += 1
+            tasks.add(asyncio.ensure_future(host_read(rr, cost)))
+        while tasks:
+            done, _ = await asyncio.wait(tasks, return_when=asyncio.FIRST_COMPLETED)
+            for d in done:
+                tasks.discard(d)
+                d.result()
+    except BaseException:
+        for t in tasks:
+            t.cancel()
+        await asyncio.gather(*tasks, return_exceptions=True)
+        raise
+    finally:
+        executor.shutdown(wait=False)
+    elapsed = max(time.monotonic() - begin, 1e-9)
+    logger.info(f"Rank {rank} finished loading. Throughput: {bytes_read / 1024**2 / elapsed:.2f}MB/s")
+
+
+def sync_execute_read_reqs(
+    read_reqs: List[ReadReq],
+    storage: StoragePlugin,
+    memory_budget_bytes: int,
+    rank: int,
+    event_loop: asyncio.AbstractEventLoop,
+) -> None:
+    event_loop.run_until_complete(
+        execute_read_reqs(read_reqs=read_reqs, storage=storage, memory_budget_bytes=memory_budget_bytes, rank=rank)
+    )
+
+
+# ------------------------------------------------------------------------------------------------
+# single-request device paths: what stage_buffer / consume_buffer do when something other than
+# the schedulers above drives them (the reference's scheduler in drop-in mode, or a test that
+# fulfils read requests directly from write requests)
+# ------------------------------------------------------------------------------------------------
+async def _retry_alloc(fn: Any, *args: Any) -> Any:
+    for _ in range(30000):
+        try:
+            return fn(*args)
+        except ArenaFull:
+            await asyncio.sleep(0.002)
+    raise _native.TsbError("timed out waiting for staging memory")
+
+
+async def stage_device_buffer(stager: Any, device: Optional[int], executor: Optional[Executor]) -> BufferType:
+    eng = get_engine(device or 0)
+    ctx = eng.ctx
+    loop = asyncio.get_running_loop()
+    nbytes = stager.staged_nbytes()
+    if nbytes == 0:
+        return memoryview(bytearray(0))
+    pbuf = await _retry_alloc(eng.pinned, nbytes)
+    probe = stager.pack_regions(0)
+    if len(probe) == 1 and len(probe[0][3]) == 0 and probe[0][2] == nbytes:
+        # one dense tensor: the D2H copy reads the tensor itself, no pack pass
+        eng.wait_current_stream(STREAM_D2H)
+        ctx.memcpy_d2h(STREAM_D2H, pbuf.ptr, probe[0][0], nbytes)
+        dptr = None
+    else:
+        dptr = await _retry_alloc(ctx.dev_alloc, nbytes)
+        eng.wait_current_stream(STREAM_PACK)
+        eng.copy_regions(stager.pack_regions(dptr), STREAM_PACK)
+        ev_pack = ctx.event_record(STREAM_PACK)
+        ctx.stream_wait_event(STREAM_D2H, ev_pack)
+        ctx.event_release(ev_pack)
+        ctx.memcpy_d2h(STREAM_D2H, pbuf.ptr, dptr, nbytes)
+    ev = ctx.event_record(STREAM_D2H)
+    try:
+        await loop.run_in_executor(executor, ctx.event_sync, ev)
+    finally:
+        ctx.event_release(ev)
+        if dptr is not None:
+            ctx.dev_free(dptr)
+    view = pbuf.view()
+    del pbuf
+    return view
+
+
+async def consume_device_buffer(consumer: Any, buf: BufferType, device: Optional[int], executor: Optional[Executor]) -> None:
+    eng = get_engine(device or 0)
+    ctx = eng.ctx
+    loop = asyncio.get_running_loop()
+    nbytes = len(buf)
+    if nbytes == 0:
+        return
+    pbuf = await _retry_alloc(eng.pinned, nbytes)
+    try:
+        await loop.run_in_executor(executor, _native.host_memcpy, pbuf.ptr, readonly_buffer_address(buf), nbytes, 0)
+        dptr = await _retry_alloc(ctx.dev_alloc, nbytes)
+        try:
+            eng.wait_current_stream(STREAM_H2D)
+            ctx.memcpy_h2d(STREAM_H2D, dptr, pbuf.ptr, nbytes)
+            ev_h2d = ctx.event_record(STREAM_H2D)
+            ctx.stream_wait_event(STREAM_PACK, ev_h2d)
+            ctx.event_release(ev_h2d)
+            eng.copy_regions(consumer.unpack_regions(dptr), STREAM_PACK)
+            ev = ctx.event_record(STREAM_PACK)
+            try:
+                await loop.run_in_executor(executor, ctx.event_sync, ev)
+            finally:
+                ctx.event_release(ev)
+        finally:
+            ctx.dev_free(dptr)
+    finally:
+        pbuf.release()

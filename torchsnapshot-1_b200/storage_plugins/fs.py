@@ -1,0 +1,76 @@
+"""Local-filesystem storage plugin.
+
+Same StoragePlugin ABI and file layout as the reference plugin (torchsnapshot/storage_plugins/
+fs.py:18-56): one file per write request under `root`, whole-file or ranged reads into a BytesIO.
+Differences are below the ABI: file I/O runs in libtsb200's pwrite/pread workers instead of
+aiofiles, and the optional `read_into` lets the scheduler read straight into pinned memory
+ -- plugins without it are served through `read` as in the reference.
+"""
+
+import asyncio
+import io
+import os
+from concurrent.futures import ThreadPoolExecutor
+from typing import Any, Dict, Optional, Set, Tuple
+
+from .. import _native, knobs
+from ..engine import buffer_address, readonly_buffer_address
+from ..io_types import ReadIO, StoragePlugin, WriteIO
+
+
+class FSStoragePlugin(StoragePlugin):
+    def __init__(self, root: str, storage_options: Optional[Dict[str, Any]] = None) -> None:
+        self.root = root
+        self._dir_cache: Set[str] = set()
+        self._executor = ThreadPoolExecutor(max_workers=16, thread_name_prefix="tsb-fs")
+        self._io_threads = knobs.get_io_threads()
+
+    def _prepare(self, rel: str) -> str:
+        path = os.path.join(self.root, rel)
+        parent = os.path.dirname(path)
+        if parent not in self._dir_cache:
+            os.makedirs(parent, exist_ok=True)
+            self._dir_cache.add(parent)
+        return path
+
+    def _write_sync(self, path: str, buf: Any) -> None:
+        n = len(buf)
+        addr = readonly_buffer_address(buf) if n else 0
+        _native.file_write(path, addr, n, self._io_threads)
+
+    async def write(self, write_io: WriteIO) -> None:
+        path = self._prepare(write_io.path)
+        await asyncio.get_running_loop().run_in_executor(self._executor, self._write_sync, path, write_io.buf)
+
+    def _read_sync(self, path: str, byte_range: Optional[Tuple[int, int]], out: Optional[memoryview]) -> bytearray:
+        if byte_range is None:
+            offset, n = 0, os.path.getsize(path)
+        else:
+            offset, n = byte_range[0], byte_range[1] - byte_range[0]
+        if out is None:
+            dst = bytearray(n)
+        else:
+            if len(out) != n:
+                raise AssertionError(f"{path}: destination holds {len(out)} bytes, the read is {n} bytes.")
+            dst = out
+        if n:
+            _native.file_read(path, offset, buffer_address(dst), n, self._io_threads)
+        return dst
+
+    async def read(self, read_io: ReadIO) -> None:
+        path = os.path.join(self.root, read_io.path)
+        data = await asyncio.get_running_loop().run_in_executor(
+            self._executor, self._read_sync, path, read_io.byte_range, None
+        )
+        read_io.buf = io.BytesIO(data)
+
+    async def read_into(self, path: str, byte_range: Optional[Tuple[int, int]], out: memoryview) -> None:
+        """Read a file (range) directly into a caller-provided writable buffer."""
+        full = os.path.join(self.root, path)
+        await asyncio.get_running_loop().run_in_executor(self._executor, self._read_sync, full, byte_range, out)
+
+    async def delete(self, path: str) -> None:
+        os.remove(os.path.join(self.root, path))
+
+    async def close(self) -> None:
+        self._executor.shutdown(wait=True)
