@@ -165,6 +165,15 @@ int tsb_stream_sync(TsbCtx* ctx, int stream);
  */
 int tsb_copy_regions(TsbCtx* ctx, int stream, const TsbRegion* regions, uint32_t n);
 
+/*
+ * Same launch, plus two events that bracket ONLY the copy kernels on the device (descriptor upload
+ * and tile-table expansion excluded): what bench.py divides the algorithmic bytes by for the
+ * roofline.  Release both with tsb_event_release.  No reference counterpart (the reference has no
+ * device timing).
+ */
+int tsb_copy_regions_timed(TsbCtx* ctx, int stream, const TsbRegion* regions, uint32_t n, TsbEvent* kernel_start,
+                           TsbEvent* kernel_stop);
+
 /* Device <-> pinned host copies on a context stream (K3 / K6). `hptr` should come from tsb_host_alloc. */
 int tsb_memcpy_d2h(TsbCtx* ctx, int stream, void* hptr, uint64_t dptr, uint64_t nbytes);
 int tsb_memcpy_h2d(TsbCtx* ctx, int stream, uint64_t dptr, const void* hptr, uint64_t nbytes);

@@ -71,6 +71,7 @@ _SIGNATURES = {
     "tsb_external_wait_stream": (_i, [_p, _u64, _i]),
     "tsb_stream_sync": (_i, [_p, _i]),
     "tsb_copy_regions": (_i, [_p, _i, _p, ctypes.c_uint32]),
+    "tsb_copy_regions_timed": (_i, [_p, _i, _p, ctypes.c_uint32, ctypes.POINTER(_u64), ctypes.POINTER(_u64)]),
     "tsb_memcpy_d2h": (_i, [_p, _i, _p, _u64, _u64]),
     "tsb_memcpy_h2d": (_i, [_p, _i, _u64, _p, _u64]),
     "tsb_memcpy_d2d": (_i, [_p, _i, _u64, _u64, _u64]),
@@ -217,6 +218,19 @@ class Context:
         if n == 0:
             return
         _check(self.lib, self.lib.tsb_copy_regions(self._h, stream, regions.ctypes.data, n))
+
+    def copy_regions_timed(self, stream: int, regions: np.ndarray) -> Tuple[int, int]:
+        """Launch and return (start, stop) events that bracket only the copy kernels."""
+        if regions.dtype != REGION_DTYPE or not regions.flags["C_CONTIGUOUS"]:
+            raise ValueError("regions must be a C-contiguous array of REGION_DTYPE")
+        a, b = _u64(), _u64()
+        _check(
+            self.lib,
+            self.lib.tsb_copy_regions_timed(
+                self._h, stream, regions.ctypes.data, int(regions.shape[0]), ctypes.byref(a), ctypes.byref(b)
+            ),
+        )
+        return a.value, b.value
 
     def memcpy_d2h(self, stream: int, hptr: int, dptr: int, nbytes: int) -> None:
         _check(self.lib, self.lib.tsb_memcpy_d2h(self._h, stream, hptr, dptr, nbytes))

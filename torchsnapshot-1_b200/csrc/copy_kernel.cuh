@@ -1,60 +1,54 @@
-// Multi-region strided copy kernel for sm_100a: the gather-pack / scatter-unpack / reshard
+// Multi-region strided copy kernels for sm_100a: the gather-pack / scatter-unpack / reshard
 // hot op of the checkpoint path (replaces the per-tensor copy_ launches of the reference,
 // torchsnapshot/batcher.py:152-155, io_preparers/tensor.py:329-338, sharded_tensor.py:296-309).
 //
-// Work decomposition: the host splits the flat payload of every region into tiles of at most
-// TSB_TILE_BYTES; a persistent grid (SMs x resident CTAs) walks the tile table with a stride of
-// gridDim.x.  Tile and region descriptors of the next iteration are prefetched into registers
-// while the current tile streams, so the dependent descriptor->data chain never sits on the
-// critical path.  All payload traffic is 16-byte vector loads/stores with the DESTINATION
-// aligned; a source whose alignment differs is read with aligned vectors and re-aligned in
-// registers with funnel shifts, so slab offsets may be arbitrary (the reference packs with no
-// padding, batcher.py:300-316).
+// Work decomposition (measured on B200, scripts/copy_variants.cu, profiles/r01_copy_variants.txt):
+// the host splits the flat payload of every region into tiles of at most TSB_TILE_BYTES and
+// launches ONE CTA PER TILE in table order, so the CTAs resident at any instant sweep a dense
+// window of the source and of the slab (6.9 TB/s r+w; a persistent grid that strides over the table
+// reaches only 6.0 TB/s, and cudaMemcpy D2D 6.55 TB/s).  A tile entry carries absolute source and
+// destination addresses, so a CTA has exactly one dependent descriptor load before it streams.
+//
+// All payload traffic is 16-byte vector loads/stores with the DESTINATION aligned; a source whose
+// alignment differs is read with aligned vectors and re-aligned in registers with funnel shifts, so
+// slab offsets may be arbitrary (the reference packs with no padding, batcher.py:300-316).
+//
+// Two kernels share the tile table format:
+//   tsb_copy_flat_kernel     contiguous runs (dense tensors, the >99% case): every thread issues
+//                            all its loads before its first store, no loop, <= 32 registers so
+//                            2048 threads stay resident per SM;
+//   tsb_copy_strided_kernel  strided boxes with short runs (non-contiguous views, reshard
+//                            overlaps): one run per warp, or one element per thread when runs are
+//                            shorter than 64 bytes.  Boxes with runs of 8 KB or more are expanded
+//                            into flat tiles by the host and go through the flat kernel.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #include "../../include/tsb200.h"
 
-#define TSB_THREADS 256
-#define TSB_CTAS_PER_SM 4
+#define TSB_FLAT_THREADS 512
+#define TSB_FLAT_UNROLL 4
+// payload bytes per tile: every thread of the flat kernel moves TSB_FLAT_UNROLL 16-byte vectors
+#define TSB_TILE_BYTES (TSB_FLAT_THREADS * TSB_FLAT_UNROLL * 16)
+
+#define TSB_STRIDED_THREADS 256
 #define TSB_UNROLL 4
-// A run at least this long is copied by the whole CTA; shorter runs go one per warp.
-#define TSB_CTA_RUN_MIN (16u * 1024u)
+// Strided regions whose runs are at least this long are expanded by the host into flat tiles (one
+// or more per run); shorter runs go to the strided kernel, one per warp.
+#define TSB_FLAT_RUN_MIN (8u * 1024u)
 // A run shorter than this is copied element-wise, one unit per thread.
 #define TSB_WARP_RUN_MIN 64u
 
-struct __align__(16) TsbTile {
-  uint64_t off;     // flat payload byte offset inside the region
-  uint32_t len;     // payload bytes in this tile
-  uint32_t region;  // index into the region table
+// One unit of work.  Flat tiles: src/dst are the absolute addresses of the tile's first byte.
+// Strided tiles: `region` indexes the region table and `off` is the flat payload offset.
+struct __align__(32) TsbTile {
+  uint64_t src;
+  uint64_t dst;
+  uint32_t len;
+  uint32_t region;
+  uint64_t off;
 };
-
-struct RegionHot {  // the fields every tile needs, prefetched into registers
-  uint64_t src, dst, run_bytes;
-  uint32_t ndim;
-};
-
-__device__ __forceinline__ TsbTile ld_tile(const TsbTile* p) {
-  uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
-  TsbTile t;
-  t.off = (uint64_t)v.x | ((uint64_t)v.y << 32);
-  t.len = v.z;
-  t.region = v.w;
-  return t;
-}
-
-__device__ __forceinline__ RegionHot ld_hot(const TsbRegion* r) {
-  const uint4* p = reinterpret_cast<const uint4*>(r);
-  uint4 a = __ldg(p);
-  uint4 b = __ldg(p + 1);
-  RegionHot h;
-  h.src = (uint64_t)a.x | ((uint64_t)a.y << 32);
-  h.dst = (uint64_t)a.z | ((uint64_t)a.w << 32);
-  h.run_bytes = (uint64_t)b.x | ((uint64_t)b.y << 32);
-  h.ndim = b.z;
-  return h;
-}
 
 // streaming 16-byte accessors: payload is touched exactly once
 __device__ __forceinline__ uint4 ld_stream(const uint4* p) { return __ldcs(p); }
@@ -72,12 +66,134 @@ __device__ __forceinline__ uint4 realign(const uint4& a, const uint4& b, uint32_
   return o;
 }
 
+// ---------------------------------------------------------------------------------------------
+// tile-table expansion (device side)
+// ---------------------------------------------------------------------------------------------
+// One contiguous run to copy; `first_tile` is the index of its first tile in the flat tile table
+// (an exclusive prefix sum the host computes), so the table can be expanded on the device and the
+// host uploads O(#runs) bytes instead of O(payload / tile) bytes.
+struct __align__(32) TsbRun {
+  uint64_t src;
+  uint64_t dst;
+  uint64_t nbytes;
+  uint64_t first_tile;
+};
+
+// Tiles of a run: the first one ends on a 16-byte boundary of the destination, the others are
+// TSB_TILE_BYTES long, so only the first tile has a head and only the last one a tail.
+__host__ __device__ __forceinline__ uint64_t tsb_first_tile_len(uint64_t dst) { return TSB_TILE_BYTES - (dst & 15u); }
+__host__ __device__ __forceinline__ uint64_t tsb_run_tiles(uint64_t dst, uint64_t nbytes) {
+  const uint64_t l0 = tsb_first_tile_len(dst);
+  if (nbytes <= l0) return nbytes ? 1 : 0;
+  return 1 + (nbytes - l0 + TSB_TILE_BYTES - 1) / TSB_TILE_BYTES;
+}
+
+__global__ void __launch_bounds__(256)
+tsb_expand_flat_kernel(const TsbRun* __restrict__ runs, uint32_t n_runs, TsbTile* __restrict__ tiles,
+                       uint32_t n_tiles) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_tiles) return;
+  // largest r with runs[r].first_tile <= t
+  uint32_t lo = 0, hi = n_runs - 1;
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi + 1) >> 1;
+    if (__ldg(&runs[mid].first_tile) <= t) lo = mid; else hi = mid - 1;
+  }
+  const uint4* rp = reinterpret_cast<const uint4*>(runs + lo);
+  const uint4 a = __ldg(rp), b = __ldg(rp + 1);
+  const uint64_t src = ((uint64_t)a.y << 32) | a.x, dst = ((uint64_t)a.w << 32) | a.z;
+  const uint64_t nbytes = ((uint64_t)b.y << 32) | b.x, first = ((uint64_t)b.w << 32) | b.z;
+  const uint64_t k = t - first;
+  const uint64_t l0 = tsb_first_tile_len(dst);
+  const uint64_t off = k == 0 ? 0 : l0 + (k - 1) * (uint64_t)TSB_TILE_BYTES;
+  uint64_t len = k == 0 ? l0 : (uint64_t)TSB_TILE_BYTES;
+  if (len > nbytes - off) len = nbytes - off;
+  const uint64_t s = src + off, d = dst + off;
+  uint4* out = reinterpret_cast<uint4*>(tiles + t);
+  out[0] = make_uint4((uint32_t)s, (uint32_t)(s >> 32), (uint32_t)d, (uint32_t)(d >> 32));
+  out[1] = make_uint4((uint32_t)len, 0xffffffffu, 0u, 0u);
+}
+
+// ---------------------------------------------------------------------------------------------
+// flat kernel
+// ---------------------------------------------------------------------------------------------
+template <int SW>
+__device__ __forceinline__ void flat_shifted(uint4* __restrict__ d4, const uint4* __restrict__ a4, uint32_t nvec,
+                                             uint32_t sb, uint32_t tid) {
+  // a4[j] and a4[j+1] both lie in aligned 16-byte granules that contain payload bytes, so the
+  // extra vector never leaves the allocation that holds the run.
+  uint4 a[TSB_FLAT_UNROLL], b[TSB_FLAT_UNROLL];
+#pragma unroll
+  for (int u = 0; u < TSB_FLAT_UNROLL; ++u) {
+    const uint32_t j = tid + u * TSB_FLAT_THREADS;
+    if (j < nvec) {
+      a[u] = __ldg(a4 + j);
+      b[u] = __ldg(a4 + j + 1);
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < TSB_FLAT_UNROLL; ++u) {
+    const uint32_t j = tid + u * TSB_FLAT_THREADS;
+    if (j < nvec) st_stream(d4 + j, realign<SW>(a[u], b[u], sb));
+  }
+}
+
+__global__ void __launch_bounds__(TSB_FLAT_THREADS)
+tsb_copy_flat_kernel(const TsbTile* __restrict__ tiles) {
+  const uint32_t tid = threadIdx.x;
+  const uint4* tp = reinterpret_cast<const uint4*>(tiles + blockIdx.x);
+  const uint4 t0 = __ldg(tp);
+  const uint32_t len = __ldg(reinterpret_cast<const uint32_t*>(tp + 1));
+  const uint8_t* src = reinterpret_cast<const uint8_t*>(((uint64_t)t0.y << 32) | t0.x);
+  uint8_t* dst = reinterpret_cast<uint8_t*>(((uint64_t)t0.w << 32) | t0.z);
+  // the host puts interior tile boundaries on 16-byte boundaries of the destination, so only the
+  // first tile of a region has a head and only the last one a tail
+  uint32_t head = (16u - ((uint32_t)(uintptr_t)dst & 15u)) & 15u;
+  if (head > len) head = len;
+  if (tid < head) dst[tid] = src[tid];
+  src += head;
+  dst += head;
+  const uint32_t n = len - head;
+  const uint32_t nvec = n >> 4;
+  const uint32_t tail = n & 15u;
+  if (tid >= TSB_FLAT_THREADS - tail) {
+    const uint32_t k = (nvec << 4) + (tid - (TSB_FLAT_THREADS - tail));
+    dst[k] = src[k];
+  }
+  uint4* d4 = reinterpret_cast<uint4*>(dst);
+  const uint32_t s = (uint32_t)(uintptr_t)src & 15u;
+  if (s == 0) {
+    const uint4* s4 = reinterpret_cast<const uint4*>(src);
+    uint4 v[TSB_FLAT_UNROLL];
+#pragma unroll
+    for (int u = 0; u < TSB_FLAT_UNROLL; ++u) {
+      const uint32_t j = tid + u * TSB_FLAT_THREADS;
+      if (j < nvec) v[u] = ld_stream(s4 + j);
+    }
+#pragma unroll
+    for (int u = 0; u < TSB_FLAT_UNROLL; ++u) {
+      const uint32_t j = tid + u * TSB_FLAT_THREADS;
+      if (j < nvec) st_stream(d4 + j, v[u]);
+    }
+  } else {
+    const uint4* a4 = reinterpret_cast<const uint4*>(src - s);
+    const uint32_t sb = (s & 3u) * 8u;
+    switch (s >> 2) {
+      case 0: flat_shifted<0>(d4, a4, nvec, sb, tid); break;
+      case 1: flat_shifted<1>(d4, a4, nvec, sb, tid); break;
+      case 2: flat_shifted<2>(d4, a4, nvec, sb, tid); break;
+      default: flat_shifted<3>(d4, a4, nvec, sb, tid); break;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// strided kernel
+// ---------------------------------------------------------------------------------------------
 template <int SW, int NL>
 __device__ __forceinline__ void copy_vec_shifted(uint4* __restrict__ d4, const uint4* __restrict__ a4,
                                                  uint64_t nvec, uint32_t sb, uint32_t lane) {
   uint64_t j = lane;
-  // a4[j] and a4[j+1] both lie in aligned 16-byte granules that contain payload bytes, so the
-  // extra vector never leaves the allocation that holds the run.
   for (; j + (uint64_t)(TSB_UNROLL - 1) * NL < nvec; j += (uint64_t)TSB_UNROLL * NL) {
     uint4 a[TSB_UNROLL], b[TSB_UNROLL];
 #pragma unroll
@@ -160,9 +276,10 @@ __device__ __forceinline__ void run_offsets(const TsbRegion* __restrict__ r, uin
 }
 
 template <typename T>
-__device__ __forceinline__ void copy_units(const TsbRegion* __restrict__ r, const RegionHot& h, uint64_t first_unit,
-                                           uint64_t nunits, uint32_t units_per_run, uint32_t tid) {
-  for (uint64_t u = tid; u < nunits; u += TSB_THREADS) {
+__device__ __forceinline__ void copy_units(const TsbRegion* __restrict__ r, uint64_t src, uint64_t dst, uint32_t ndim,
+                                           uint64_t first_unit, uint64_t nunits, uint32_t units_per_run,
+                                           uint32_t tid) {
+  for (uint64_t u = tid; u < nunits; u += TSB_STRIDED_THREADS) {
     const uint64_t f = first_unit + u;
     uint64_t q, k;
     if ((f >> 32) == 0) {
@@ -173,91 +290,55 @@ __device__ __forceinline__ void copy_units(const TsbRegion* __restrict__ r, cons
       k = f % units_per_run;
     }
     int64_t so, dofs;
-    run_offsets(r, h.ndim, q, so, dofs);
-    const T* sp = reinterpret_cast<const T*>(h.src + so) + k;
-    T* dp = reinterpret_cast<T*>(h.dst + dofs) + k;
+    run_offsets(r, ndim, q, so, dofs);
+    const T* sp = reinterpret_cast<const T*>(src + so) + k;
+    T* dp = reinterpret_cast<T*>(dst + dofs) + k;
     *dp = *sp;
   }
 }
 
-__device__ __forceinline__ void process_tile(const TsbTile& t, const RegionHot& h, const TsbRegion* __restrict__ r,
-                                             uint32_t tid) {
-  if (h.ndim == 0) {
-    copy_span<TSB_THREADS>(reinterpret_cast<uint8_t*>(h.dst + t.off), reinterpret_cast<const uint8_t*>(h.src + t.off),
-                           t.len, tid);
-    return;
-  }
-  if (h.run_bytes >= TSB_CTA_RUN_MIN) {
-    uint64_t q = t.off / h.run_bytes;
-    uint64_t inner = t.off - q * h.run_bytes;
-    uint64_t remaining = t.len;
-    while (remaining) {
-      uint64_t piece = h.run_bytes - inner;
-      if (piece > remaining) piece = remaining;
-      int64_t so, dofs;
-      run_offsets(r, h.ndim, q, so, dofs);
-      copy_span<TSB_THREADS>(reinterpret_cast<uint8_t*>(h.dst + dofs + inner),
-                             reinterpret_cast<const uint8_t*>(h.src + so + inner), piece, tid);
-      remaining -= piece;
-      inner = 0;
-      ++q;
-    }
-    return;
-  }
-  if (h.run_bytes >= TSB_WARP_RUN_MIN) {
+__global__ void __launch_bounds__(TSB_STRIDED_THREADS)
+tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __restrict__ tiles) {
+  const uint32_t tid = threadIdx.x;
+  const uint4* tp = reinterpret_cast<const uint4*>(tiles + blockIdx.x);
+  const uint4 t1 = __ldg(tp + 1);
+  const uint32_t len = t1.x;
+  const uint64_t off = ((uint64_t)t1.w << 32) | t1.z;
+  const TsbRegion* r = regions + t1.y;
+  const uint4* rp = reinterpret_cast<const uint4*>(r);
+  const uint4 ra = __ldg(rp);
+  const uint4 rb = __ldg(rp + 1);
+  const uint64_t src = ((uint64_t)ra.y << 32) | ra.x;
+  const uint64_t dst = ((uint64_t)ra.w << 32) | ra.z;
+  const uint64_t run_bytes = ((uint64_t)rb.y << 32) | rb.x;
+  const uint32_t ndim = rb.z;
+
+  // runs of TSB_FLAT_RUN_MIN bytes or more never get here: the host expands them into flat tiles
+  if (run_bytes >= TSB_WARP_RUN_MIN) {
     // the host emits whole runs per tile for this class
-    const uint64_t q0 = t.off / h.run_bytes;
-    const uint32_t nruns = t.len / (uint32_t)h.run_bytes;
+    const uint64_t q0 = off / run_bytes;
+    const uint32_t nruns = len / (uint32_t)run_bytes;
     const uint32_t warp = tid >> 5, lane = tid & 31u;
-    for (uint32_t i = warp; i < nruns; i += TSB_THREADS / 32) {
+    for (uint32_t i = warp; i < nruns; i += TSB_STRIDED_THREADS / 32) {
       int64_t so, dofs;
-      run_offsets(r, h.ndim, q0 + i, so, dofs);
-      copy_span<32>(reinterpret_cast<uint8_t*>(h.dst + dofs), reinterpret_cast<const uint8_t*>(h.src + so),
-                    h.run_bytes, lane);
+      run_offsets(r, ndim, q0 + i, so, dofs);
+      copy_span<32>(reinterpret_cast<uint8_t*>(dst + dofs), reinterpret_cast<const uint8_t*>(src + so), run_bytes,
+                    lane);
     }
     return;
   }
   // element mode: the widest power-of-two unit every address of the region is aligned to
-  uint64_t m = h.src | h.dst | h.run_bytes | 16u;
-  for (uint32_t d = 0; d < h.ndim; ++d)
-    m |= (uint64_t)__ldg(&r->src_stride[d]) | (uint64_t)__ldg(&r->dst_stride[d]);
+  uint64_t m = src | dst | run_bytes | 16u;
+  for (uint32_t d = 0; d < ndim; ++d) m |= (uint64_t)__ldg(&r->src_stride[d]) | (uint64_t)__ldg(&r->dst_stride[d]);
   const uint32_t unit = (uint32_t)(m & (~m + 1));  // lowest set bit: 1, 2, 4, 8 or 16
-  const uint32_t upr = (uint32_t)h.run_bytes / unit;
-  const uint64_t first = t.off / unit;
-  const uint64_t nunits = t.len / unit;
+  const uint32_t upr = (uint32_t)run_bytes / unit;
+  const uint64_t first = off / unit;
+  const uint64_t nunits = len / unit;
   switch (unit) {
-    case 1: copy_units<uint8_t>(r, h, first, nunits, upr, tid); break;
-    case 2: copy_units<uint16_t>(r, h, first, nunits, upr, tid); break;
-    case 4: copy_units<uint32_t>(r, h, first, nunits, upr, tid); break;
-    case 8: copy_units<uint2>(r, h, first, nunits, upr, tid); break;
-    default: copy_units<uint4>(r, h, first, nunits, upr, tid); break;
-  }
-}
-
-__global__ void __launch_bounds__(TSB_THREADS, TSB_CTAS_PER_SM)
-tsb_copy_regions_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __restrict__ tiles, uint32_t n_tiles) {
-  const uint32_t tid = threadIdx.x;
-  const uint64_t stride = gridDim.x;
-  uint64_t t = blockIdx.x;
-  if (t >= n_tiles) return;
-  TsbTile cur = ld_tile(tiles + t);
-  RegionHot hot = ld_hot(regions + cur.region);
-  bool has_next = t + stride < n_tiles;
-  TsbTile nxt = cur;
-  if (has_next) nxt = ld_tile(tiles + t + stride);
-  for (;;) {
-    // prefetch: tile entry two iterations ahead, region header one iteration ahead
-    const bool has_nn = has_next && (t + 2 * stride < n_tiles);
-    TsbTile nn = nxt;
-    RegionHot nhot = hot;
-    if (has_nn) nn = ld_tile(tiles + t + 2 * stride);
-    if (has_next) nhot = ld_hot(regions + nxt.region);
-    process_tile(cur, hot, regions + cur.region, tid);
-    if (!has_next) break;
-    cur = nxt;
-    hot = nhot;
-    nxt = nn;
-    has_next = has_nn;
-    t += stride;
+    case 1: copy_units<uint8_t>(r, src, dst, ndim, first, nunits, upr, tid); break;
+    case 2: copy_units<uint16_t>(r, src, dst, ndim, first, nunits, upr, tid); break;
+    case 4: copy_units<uint32_t>(r, src, dst, ndim, first, nunits, upr, tid); break;
+    case 8: copy_units<uint2>(r, src, dst, ndim, first, nunits, upr, tid); break;
+    default: copy_units<uint4>(r, src, dst, ndim, first, nunits, upr, tid); break;
   }
 }

@@ -19,9 +19,8 @@
 #include "copy_kernel.cuh"
 
 static_assert(sizeof(TsbRegion) == 128, "TsbRegion must be 128 bytes");
-static_assert(sizeof(TsbTile) == 16, "TsbTile must be 16 bytes");
-
-#define TSB_TILE_BYTES (64u * 1024u)
+static_assert(sizeof(TsbTile) == 32, "TsbTile must be 32 bytes");
+static_assert(sizeof(TsbRun) == 32, "TsbRun must be 32 bytes");
 
 // ------------------------------------------------------------------------------------------
 // errors
@@ -216,7 +215,6 @@ struct PendingScratch {
 struct TsbCtx {
   int device = 0;
   int sm_count = 0;
-  int ctas_per_sm = TSB_CTAS_PER_SM;
   cudaStream_t streams[TSB_NUM_STREAMS] = {};
   Arena* host_arena = nullptr;
   Arena* dev_arena = nullptr;
@@ -282,7 +280,7 @@ static void reap_scratch(TsbCtx* ctx, bool wait_all) {
 }
 
 // ------------------------------------------------------------------------------------------
-// tile table
+// tile tables
 // ------------------------------------------------------------------------------------------
 static int validate_region(const TsbRegion& r, uint32_t i) {
   if (r.ndim > TSB_MAX_DIMS) return set_err(TSB_EINVAL, "region %u: ndim %u > %d", i, r.ndim, TSB_MAX_DIMS);
@@ -302,7 +300,26 @@ static bool region_payload(const TsbRegion& r, uint64_t* total) {
   return true;
 }
 
-static int build_tiles(const TsbRegion* regions, uint32_t n, std::vector<TsbTile>& tiles) {
+// Queue one contiguous run; its tiles are expanded on the device (tsb_expand_flat_kernel).
+static void flat_run(uint64_t src, uint64_t dst, uint64_t n, std::vector<TsbRun>& runs, uint64_t* n_tiles) {
+  if (n == 0) return;
+  TsbRun r;
+  r.src = src;
+  r.dst = dst;
+  r.nbytes = n;
+  r.first_tile = *n_tiles;
+  runs.push_back(r);
+  *n_tiles += tsb_run_tiles(dst, n);
+}
+
+struct TilePlan {
+  std::vector<TsbRun> flat_runs;
+  uint64_t flat_tiles = 0;
+  std::vector<TsbTile> strided;
+  std::vector<TsbRegion> strided_regions;
+};
+
+static int build_tiles(const TsbRegion* regions, uint32_t n, TilePlan& plan) {
   for (uint32_t i = 0; i < n; ++i) {
     const TsbRegion& r = regions[i];
     int rc = validate_region(r, i);
@@ -310,19 +327,42 @@ static int build_tiles(const TsbRegion* regions, uint32_t n, std::vector<TsbTile
     uint64_t total;
     if (!region_payload(r, &total)) return set_err(TSB_EINVAL, "region %u: size overflow", i);
     if (total == 0) continue;
-    uint64_t step = TSB_TILE_BYTES;
-    if (r.ndim > 0 && r.run_bytes < TSB_CTA_RUN_MIN) {
-      // warp / element classes: tiles hold whole runs
-      uint64_t runs = TSB_TILE_BYTES / r.run_bytes;
-      if (runs == 0) runs = 1;
-      step = runs * r.run_bytes;
+    if (r.ndim == 0) {
+      flat_run(r.src, r.dst, r.run_bytes, plan.flat_runs, &plan.flat_tiles);
+      continue;
     }
+    if (r.run_bytes >= TSB_FLAT_RUN_MIN) {
+      // long runs: every run is a contiguous copy of its own
+      uint64_t idx[TSB_MAX_DIMS] = {0, 0, 0, 0};
+      const uint64_t runs = total / r.run_bytes;
+      for (uint64_t q = 0; q < runs; ++q) {
+        int64_t so = 0, dofs = 0;
+        for (uint32_t d = 0; d < r.ndim; ++d) {
+          so += (int64_t)idx[d] * r.src_stride[d];
+          dofs += (int64_t)idx[d] * r.dst_stride[d];
+        }
+        flat_run(r.src + so, r.dst + dofs, r.run_bytes, plan.flat_runs, &plan.flat_tiles);
+        for (int d = (int)r.ndim - 1; d >= 0; --d) {
+          if (++idx[d] < r.size[d]) break;
+          idx[d] = 0;
+        }
+      }
+      continue;
+    }
+    // short runs: tiles hold whole runs; the strided kernel walks them
+    const uint32_t ridx = (uint32_t)plan.strided_regions.size();
+    plan.strided_regions.push_back(r);
+    uint64_t runs_per_tile = TSB_TILE_BYTES / r.run_bytes;
+    if (runs_per_tile == 0) runs_per_tile = 1;
+    const uint64_t step = runs_per_tile * r.run_bytes;
     for (uint64_t off = 0; off < total; off += step) {
       TsbTile t;
+      t.src = 0;
+      t.dst = 0;
       t.off = off;
       t.len = (uint32_t)std::min<uint64_t>(step, total - off);
-      t.region = i;
-      tiles.push_back(t);
+      t.region = ridx;
+      plan.strided.push_back(t);
     }
   }
   return TSB_OK;
@@ -365,12 +405,6 @@ int tsb_ctx_create(int device, uint64_t host_arena_max, uint64_t dev_arena_max, 
       return set_err(TSB_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e));
     }
   }
-  int occ = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tsb_copy_regions_kernel, TSB_THREADS, 0) == cudaSuccess &&
-      occ > 0)
-    ctx->ctas_per_sm = occ;
-  else
-    (void)cudaGetLastError();
   if (host_arena_max == 0) host_arena_max = 4ull << 30;
   if (dev_arena_max == 0) dev_arena_max = 16ull << 30;
   ctx->host_arena = new Arena(true, host_arena_max, 256ull << 20, 4096);
@@ -568,40 +602,60 @@ int tsb_stream_sync(TsbCtx* ctx, int stream) {
   return TSB_OK;
 }
 
-int tsb_copy_regions(TsbCtx* ctx, int stream, const TsbRegion* regions, uint32_t n) {
+static int copy_regions_impl(TsbCtx* ctx, int stream, const TsbRegion* regions, uint32_t n, const TsbEvent* kernel_start,
+                             const TsbEvent* kernel_stop) {
   CHECK_CTX(ctx);
   CHECK_STREAM(stream);
   if (n == 0) return TSB_OK;
   if (!regions) return set_err(TSB_EINVAL, "null regions");
   reap_scratch(ctx, false);
-  std::vector<TsbTile> tiles;
-  tiles.reserve(n + 1024);
-  int rc = build_tiles(regions, n, tiles);
+  TilePlan plan;
+  plan.flat_runs.reserve(n);
+  int rc = build_tiles(regions, n, plan);
   if (rc != TSB_OK) return rc;
-  if (tiles.empty()) return TSB_OK;
-  if (tiles.size() > 0xffffffffull) return set_err(TSB_EINVAL, "too many tiles in one launch");
-  const uint64_t reg_bytes = (uint64_t)n * sizeof(TsbRegion);
-  const uint64_t tile_bytes = (uint64_t)tiles.size() * sizeof(TsbTile);
-  const uint64_t total = reg_bytes + tile_bytes;
+  if (plan.flat_runs.empty() && plan.strided.empty()) return TSB_OK;
+  if (plan.flat_tiles > 0x7fffffffull || plan.strided.size() > 0x7fffffffull)
+    return set_err(TSB_EINVAL, "too many tiles in one launch");
+  // uploaded scratch: [flat runs][strided tiles][strided regions]; device-only: [flat tiles]
+  const uint64_t run_bytes = (uint64_t)plan.flat_runs.size() * sizeof(TsbRun);
+  const uint64_t str_bytes = (uint64_t)plan.strided.size() * sizeof(TsbTile);
+  const uint64_t reg_bytes = (uint64_t)plan.strided_regions.size() * sizeof(TsbRegion);
+  const uint64_t upload = run_bytes + str_bytes + reg_bytes;
+  const uint64_t tile_bytes = plan.flat_tiles * sizeof(TsbTile);
   uint64_t hbuf = 0, dbuf = 0;
-  rc = ctx->host_arena->alloc(total, &hbuf);
+  rc = ctx->host_arena->alloc(upload, &hbuf);
   if (rc != TSB_OK) return rc;
-  rc = ctx->dev_arena->alloc(total, &dbuf);
+  rc = ctx->dev_arena->alloc(upload + tile_bytes, &dbuf);
   if (rc != TSB_OK) {
     ctx->host_arena->free(hbuf);
     return rc;
   }
-  memcpy((void*)(uintptr_t)hbuf, regions, reg_bytes);
-  memcpy((void*)(uintptr_t)(hbuf + reg_bytes), tiles.data(), tile_bytes);
+  char* h = (char*)(uintptr_t)hbuf;
+  if (run_bytes) memcpy(h, plan.flat_runs.data(), run_bytes);
+  if (str_bytes) memcpy(h + run_bytes, plan.strided.data(), str_bytes);
+  if (reg_bytes) memcpy(h + run_bytes + str_bytes, plan.strided_regions.data(), reg_bytes);
   cudaStream_t s = ctx->streams[stream];
-  cudaError_t e = cudaMemcpyAsync((void*)(uintptr_t)dbuf, (void*)(uintptr_t)hbuf, total, cudaMemcpyHostToDevice, s);
-  if (e == cudaSuccess) {
-    const uint32_t n_tiles = (uint32_t)tiles.size();
-    const uint32_t grid = (uint32_t)std::min<uint64_t>(n_tiles, (uint64_t)ctx->sm_count * ctx->ctas_per_sm);
-    tsb_copy_regions_kernel<<<grid, TSB_THREADS, 0, s>>>((const TsbRegion*)(uintptr_t)dbuf,
-                                                         (const TsbTile*)(uintptr_t)(dbuf + reg_bytes), n_tiles);
+  cudaError_t e = cudaMemcpyAsync((void*)(uintptr_t)dbuf, h, upload, cudaMemcpyHostToDevice, s);
+  cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+  if (e == cudaSuccess && plan.flat_tiles) {
+    const uint32_t nt = (uint32_t)plan.flat_tiles;
+    TsbTile* tiles = (TsbTile*)(uintptr_t)(dbuf + upload);
+    tsb_expand_flat_kernel<<<(nt + 255) / 256, 256, 0, s>>>((const TsbRun*)(uintptr_t)dbuf,
+                                                            (uint32_t)plan.flat_runs.size(), tiles, nt);
+    if (kernel_start) {
+      if (event_lookup(ctx, *kernel_start, &ev_start) == TSB_OK) cudaEventRecord(ev_start, s);
+    }
+    tsb_copy_flat_kernel<<<nt, TSB_FLAT_THREADS, 0, s>>>(tiles);
+    e = cudaGetLastError();
+  } else if (kernel_start && event_lookup(ctx, *kernel_start, &ev_start) == TSB_OK) {
+    cudaEventRecord(ev_start, s);
+  }
+  if (e == cudaSuccess && !plan.strided.empty()) {
+    tsb_copy_strided_kernel<<<(uint32_t)plan.strided.size(), TSB_STRIDED_THREADS, 0, s>>>(
+        (const TsbRegion*)(uintptr_t)(dbuf + run_bytes + str_bytes), (const TsbTile*)(uintptr_t)(dbuf + run_bytes));
     e = cudaGetLastError();
   }
+  if (kernel_stop && event_lookup(ctx, *kernel_stop, &ev_stop) == TSB_OK) cudaEventRecord(ev_stop, s);
   // the scratch is released once the launch has completed
   PendingScratch p;
   p.hbuf = hbuf;
@@ -627,6 +681,22 @@ int tsb_copy_regions(TsbCtx* ctx, int stream, const TsbRegion* regions, uint32_t
   }
   if (e != cudaSuccess) return set_err(TSB_ECUDA, "copy_regions launch failed: %s", cudaGetErrorString(e));
   return TSB_OK;
+}
+
+int tsb_copy_regions(TsbCtx* ctx, int stream, const TsbRegion* regions, uint32_t n) {
+  return copy_regions_impl(ctx, stream, regions, n, nullptr, nullptr);
+}
+
+int tsb_copy_regions_timed(TsbCtx* ctx, int stream, const TsbRegion* regions, uint32_t n, TsbEvent* kernel_start,
+                           TsbEvent* kernel_stop) {
+  if (!ctx || !kernel_start || !kernel_stop) return set_err(TSB_EINVAL, "null argument");
+  // allocate the two event handles first (recorded on an idle point of the stream, then re-recorded
+  // around the copy kernels inside the launch)
+  int rc = tsb_event_record(ctx, stream, kernel_start);
+  if (rc != TSB_OK) return rc;
+  rc = tsb_event_record(ctx, stream, kernel_stop);
+  if (rc != TSB_OK) return rc;
+  return copy_regions_impl(ctx, stream, regions, n, kernel_start, kernel_stop);
 }
 
 int tsb_memcpy_d2h(TsbCtx* ctx, int stream, void* hptr, uint64_t dptr, uint64_t nbytes) {

@@ -80,6 +80,12 @@ class Engine:
         self.ctx.copy_regions(stream, arr)
         self.launches += 1
 
+    def copy_region_array_timed(self, arr: np.ndarray, stream: int = STREAM_PACK):
+        """Launch; returns (start, stop) events around the copy kernels only (caller releases)."""
+        ev = self.ctx.copy_regions_timed(stream, arr)
+        self.launches += 1
+        return ev
+
     def wait_current_stream(self, stream: int) -> None:
         """Order a context stream after the work already queued on torch's current stream."""
         with torch.cuda.device(self.device):
