@@ -1,0 +1,238 @@
+"""End-to-end take / restore / read_object of CUDA state through the B200 path, against the
+reference-made fixtures and the CPU oracle.  Bit-exact comparisons."""
+
+import asyncio
+import hashlib
+import io
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import _cases
+import oracle
+from test_snapshot_cpu import _c1_app_state, _normalise, _payloads
+from torchsnapshot_b200 import knobs
+from torchsnapshot_b200.io_types import ReadIO, StoragePlugin, WriteIO
+from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+pytestmark = pytest.mark.gpu
+
+
+def sha(b) -> str:
+    return hashlib.sha256(bytes(b)).hexdigest()
+
+
+def _bytes(t: torch.Tensor) -> bytes:
+    return oracle.serialize(t.detach().cpu())
+
+
+def _to_cuda(app_state):
+    app_state["model"].cuda()
+    optim = app_state["optim"]
+    for st in optim.state.values():
+        for k, v in st.items():
+            if isinstance(v, torch.Tensor):
+                st[k] = v.cuda()
+    return app_state
+
+
+def test_c1_on_gpu_matches_reference_snapshot(golden_dir, tmp_path, engine):
+    """BASELINE config 0 with the state on the GPU: payload bytes and manifest equal the snapshot
+    the reference wrote for the same state."""
+    ref_root = os.path.join(golden_dir, "c1_simple", "snapshot")
+    app_state = _to_cuda(_c1_app_state())
+    launches = engine.launches
+    ours = str(tmp_path / "snap")
+    Snapshot.take(ours, app_state)
+    assert engine.launches > launches, "the CUDA path did not run"
+    ref_payloads, ref_meta = _payloads(ref_root)
+    our_payloads, our_meta = _payloads(ours)
+    assert our_payloads == ref_payloads
+    assert _normalise(our_meta) == _normalise(ref_meta)
+    # restore the reference-written snapshot into CUDA state
+    inputs = torch.load(os.path.join(golden_dir, "c1_simple", "inputs.pt"), weights_only=False)
+    fresh = _to_cuda(_c1_app_state(seed=7))
+    Snapshot(ref_root).restore(fresh)
+    for name, t in fresh["model"].state_dict().items():
+        assert t.is_cuda and _bytes(t) == oracle.serialize(inputs["tensors"][f"model/{name}"])
+    st = fresh["optim"].state_dict()["state"]
+    assert _bytes(st[2]["exp_avg_sq"]) == oracle.serialize(inputs["tensors"]["optim/state/2/exp_avg_sq"])
+
+
+@pytest.mark.parametrize("case", ["mixed", "threshold"])
+def test_gpu_take_matches_reference_fixture(golden_dir, tmp_path, case):
+    gold = json.load(open(os.path.join(golden_dir, f"slab_{case}.json")))
+    threshold, items = getattr(_cases, f"slab_case_{case}")()
+    state = StateDict({p: _cases.build_view(spec, "cuda") for p, spec in items})
+    with knobs.override_slab_size_threshold_bytes(threshold):
+        snap = Snapshot.take(str(tmp_path / "s"), {"st": state})
+    payloads, meta = _payloads(str(tmp_path / "s"))
+    slab_names = []
+    for p, _spec in items:
+        e = meta["manifest"][f"0/st/{p}"]
+        g = gold["objects"][p]
+        assert payloads[f"0/st/{p}"] == g["sha256"], p
+        assert e["byte_range"] == g["byte_range"] and e["shape"] == g["shape"] and e["dtype"] == g["dtype"]
+        if g["slab"] is not None:
+            if e["location"] not in slab_names:
+                slab_names.append(e["location"])
+            assert slab_names.index(e["location"]) == g["slab"]
+    for name, g in zip(slab_names, gold["slabs"]):
+        blob = open(os.path.join(str(tmp_path / "s"), name), "rb").read()
+        assert len(blob) == g["size"] and sha(blob) == g["sha256"]
+    # restore into strided CUDA twins
+    out = StateDict({p: _cases.build_view({**spec, "seed": spec["seed"] + 5}, "cuda") for p, spec in items})
+    snap.restore({"st": out})
+    for p, _spec in items:
+        assert _bytes(out[p]) == _bytes(state[p]), p
+    # read_object of one member of a slab, tiled
+    obj = snap.read_object("0/st/big_f32" if case == "mixed" else "0/st/over_threshold",
+                           obj_out=torch.zeros_like(state["big_f32" if case == "mixed" else "over_threshold"]),
+                           memory_budget_bytes=10000)
+    assert _bytes(obj) == _bytes(state["big_f32" if case == "mixed" else "over_threshold"])
+
+
+class _Fake:
+    def __init__(self, boxes, dtype, shape, device, full=None):
+        from types import SimpleNamespace as NS
+
+        self._shape = list(shape)
+        self._shards = []
+        for o, s in boxes:
+            t = (_cases.box_slice(full, (o, s)).contiguous() if full is not None else torch.zeros(s, dtype=dtype)).to(device)
+            self._shards.append(NS(tensor=t, metadata=NS(shard_offsets=list(o), shard_sizes=list(s))))
+
+    def local_shards(self):
+        return self._shards
+
+
+def test_gpu_reshard_all_layout_pairs(golden_dir, monkeypatch):
+    """Persisted pieces (host bytes) -> pinned -> H2D -> strided box kernel into CUDA shards, for every
+    src x dst layout of the reference-made reshard fixture."""
+    import torchsnapshot_b200.io_preparer as iop
+    from test_host_planner import _sharded_entry, run
+
+    gold = json.load(open(os.path.join(golden_dir, "sharded.json")))
+    shape = _cases.SHARD_GLOBAL_SHAPE
+    full = _cases.raw_tensor(_cases.SHARD_SEED, shape, _cases.DTYPES[_cases.SHARD_DTYPE])
+    layouts = _cases.shard_layouts(shape)
+    monkeypatch.setattr(iop, "_is_sharded_tensor", lambda o: isinstance(o, _Fake))
+    monkeypatch.setattr(_Fake, "metadata", lambda self: type("M", (), {"size": self._shape})(), raising=False)
+    for key, g in gold["reshard"].items():
+        src_name, dst_name = key.split("->")
+        # stage the source pieces from CUDA shards (pack kernel when the piece is a strided view)
+        dim, boxes = layouts[src_name]
+        shards, wrs = [], []
+        for off, sizes in boxes:
+            local = _cases.box_slice(full, (off, sizes)).contiguous().cuda()
+            for tensor, o, s in iop.ShardedTensorIOPreparer.subdivide_shard(local, list(off), list(sizes), dim,
+                                                                            _cases.SHARD_MAX_BYTES):
+                e, w = iop.TensorIOPreparer.prepare_write(f"sharded/foo_{'_'.join(map(str, o))}", tensor)
+                shards.append(iop.Shard(offsets=o, sizes=s, tensor=e))
+                wrs += w
+        entry = iop.ShardedTensorEntry(shards=shards)
+        staged = {wr.path: bytes(run(wr.buffer_stager.stage_buffer())) for wr in wrs}
+        assert [sha(staged[s.tensor.location]) for s in entry.shards] == [p["sha256"] for p in gold["writes"][src_name]["pieces"]]
+        dst = _Fake(layouts[dst_name][1], full.dtype, shape, "cuda")
+        rrs, _ = iop.ShardedTensorIOPreparer.prepare_read(entry, dst)
+        for rr in rrs:
+            assert rr.buffer_consumer.is_device_consumable()
+            run(rr.buffer_consumer.consume_buffer(staged[rr.path]))
+        assert [sha(_bytes(s.tensor)) for s in dst.local_shards()] == g["dst_sha256"], key
+
+
+def test_waves_and_small_arenas(tmp_path, monkeypatch):
+    """A device staging bound smaller than the payload forces several pack waves; a pinned bound of a few
+    slabs forces the D2H pipeline to wait for storage writes.  Result must be unchanged."""
+    from torchsnapshot_b200 import engine as engmod
+
+    engmod.shutdown_engines()
+    monkeypatch.setenv("TSB200_DEVICE_STAGING_BYTES", str(96 << 20))
+    monkeypatch.setenv("TSB200_PINNED_BYTES", str(24 << 20))
+    try:
+        g = torch.Generator(device="cuda").manual_seed(0)
+        state = StateDict({f"t{i}": torch.randint(0, 255, (int(n),), dtype=torch.uint8, device="cuda", generator=g)
+                           for i, n in enumerate(np.random.RandomState(0).randint(1, 3 << 20, size=60))})
+        state["big"] = torch.randint(0, 255, (20 << 20,), dtype=torch.uint8, device="cuda", generator=g)
+        with knobs.override_slab_size_threshold_bytes(8 << 20):
+            snap = Snapshot.take(str(tmp_path / "s"), {"st": state})
+            out = StateDict({k: torch.zeros_like(v) for k, v in state.items()})
+            snap.restore({"st": out})
+        for k in state:
+            assert torch.equal(out[k], state[k]), k
+    finally:
+        engmod.shutdown_engines()
+
+
+def test_async_take_is_consistent_under_mutation(tmp_path):
+    g = torch.Generator(device="cuda").manual_seed(1)
+    state = StateDict({f"t{i}": torch.randn(1 << 18, device="cuda", generator=g) for i in range(40)})
+    want = {k: v.clone() for k, v in state.items()}
+    pending = Snapshot.async_take(str(tmp_path / "s"), {"st": state})
+    for v in state.values():
+        v.zero_()  # training continues and overwrites the parameters
+    snap = pending.wait()
+    out = StateDict({k: torch.zeros_like(v) for k, v in state.items()})
+    snap.restore({"st": out})
+    for k in want:
+        assert torch.equal(out[k], want[k]), k
+
+
+class _MemPlugin(StoragePlugin):
+    """A third-party style plugin: plain StoragePlugin ABI, no read_into (bytes come back in a BytesIO)."""
+
+    def __init__(self):
+        self.files = {}
+
+    async def write(self, write_io: WriteIO) -> None:
+        assert isinstance(write_io.buf, (bytes, memoryview))
+        self.files[write_io.path] = bytes(write_io.buf)
+
+    async def read(self, read_io: ReadIO) -> None:
+        data = self.files[read_io.path]
+        if read_io.byte_range is not None:
+            data = data[read_io.byte_range[0] : read_io.byte_range[1]]
+        read_io.buf = io.BytesIO(data)
+
+    async def delete(self, path: str) -> None:
+        del self.files[path]
+
+    async def close(self) -> None:
+        pass
+
+
+def test_third_party_storage_plugin_abi(monkeypatch):
+    import torchsnapshot_b200.snapshot as snapmod
+
+    plugin = _MemPlugin()
+    monkeypatch.setattr(snapmod, "url_to_storage_plugin", lambda path, opts=None: plugin)
+    threshold, items = _cases.slab_case_mixed()
+    state = StateDict({p: _cases.build_view(spec, "cuda") for p, spec in items})
+    snap = Snapshot.take("mem://x", {"st": state})
+    assert ".snapshot_metadata" in plugin.files
+    out = StateDict({p: torch.zeros_like(t) for p, t in state.items()})
+    snap.restore({"st": out})
+    for p in state:
+        assert _bytes(out[p]) == _bytes(state[p]), p
+
+
+def test_non_batched_large_tensors_and_chunks(tmp_path):
+    g = torch.Generator(device="cuda").manual_seed(2)
+    big = torch.randn(1000, 999, device="cuda", generator=g)          # > slab threshold below: written on its own
+    huge = torch.randn(4000, 1000, device="cuda", generator=g)         # > chunk size below: chunked
+    view = torch.randn(3000, 1200, device="cuda", generator=g)[:, 100:1100]  # strided and unbatched
+    state = StateDict(big=big, huge=huge, view=view, small=torch.arange(5, device="cuda"))
+    with knobs.override_slab_size_threshold_bytes(1 << 20), knobs.override_max_chunk_size_bytes(6 << 20):
+        snap = Snapshot.take(str(tmp_path / "s"), {"st": state})
+        m = snap.get_manifest()
+        assert m["0/st/big"].location == "0/st/big" and m["0/st/huge"].type == "ChunkedTensor"
+        assert open(os.path.join(str(tmp_path / "s"), "0/st/big"), "rb").read() == _bytes(big)
+        assert open(os.path.join(str(tmp_path / "s"), "0/st/view"), "rb").read() == _bytes(view)
+        out = StateDict(big=torch.zeros_like(big), huge=torch.zeros_like(huge), view=torch.zeros(3000, 1000, device="cuda"),
+                        small=torch.zeros(5, dtype=torch.int64, device="cuda"))
+        snap.restore({"st": out})
+    for k in state:
+        assert torch.equal(out[k], state[k]), k

@@ -1,0 +1,194 @@
+"""Snapshot.take / restore / read_object / async_take on CPU tensors (host path) and drop-in
+compatibility with a snapshot the reference wrote (tests/golden/c1_simple, BASELINE config 0)."""
+
+import hashlib
+import json
+import os
+import re
+from collections import OrderedDict
+
+import pytest
+import torch
+
+import oracle
+from torchsnapshot_b200 import knobs
+from torchsnapshot_b200.manifest import SnapshotMetadata
+from torchsnapshot_b200.rng_state import RNGState
+from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+
+def sha(b) -> str:
+    return hashlib.sha256(bytes(b)).hexdigest()
+
+
+def _c1_app_state(seed=1234, step=True):
+    torch.manual_seed(seed)
+    model = torch.nn.Sequential(torch.nn.Linear(128, 64), torch.nn.Linear(64, 32), torch.nn.Linear(32, 1))
+    optim = torch.optim.Adam(model.parameters(), lr=1e-3)
+    if step:
+        model(torch.randn(16, 128)).sum().backward()
+        optim.step()
+    return {"model": model, "optim": optim, "progress": StateDict(current_epoch=0)}
+
+
+def _payloads(root):
+    """{manifest path: sha256 of payload bytes} for every tensor entry of a snapshot directory."""
+    meta = json.load(open(os.path.join(root, ".snapshot_metadata")))
+    out = {}
+    for path, e in meta["manifest"].items():
+        if e["type"] != "Tensor":
+            continue
+        with open(os.path.join(root, e["location"]), "rb") as f:
+            buf = f.read()
+        br = e["byte_range"]
+        out[path] = sha(buf if br is None else buf[br[0] : br[1]])
+    return out, meta
+
+
+def _normalise(meta):
+    """Manifest with slab uuids factored out (slab names are random, reference batcher.py:172)."""
+    text = json.dumps(meta, sort_keys=True)
+    names = []
+    for m in re.finditer(r"batched/[0-9a-f-]{36}", text):
+        if m.group(0) not in names:
+            names.append(m.group(0))
+    for i, n in enumerate(names):
+        text = text.replace(n, f"batched/#{i}")
+    return json.loads(text)
+
+
+def test_take_writes_what_the_reference_wrote(golden_dir, tmp_path):
+    """Same app state -> same manifest (modulo slab uuids) and the same payload bytes per object."""
+    ref_root = os.path.join(golden_dir, "c1_simple", "snapshot")
+    ours = str(tmp_path / "snap")
+    Snapshot.take(ours, _c1_app_state())
+    ref_payloads, ref_meta = _payloads(ref_root)
+    our_payloads, our_meta = _payloads(ours)
+    assert our_payloads == ref_payloads
+    assert _normalise(our_meta) == _normalise(ref_meta)
+    # the object files (pickled tuples etc.) are there as well
+    for path, e in ref_meta["manifest"].items():
+        if e["type"] == "object":
+            assert os.path.exists(os.path.join(ours, e["location"]))
+
+
+def test_restore_from_a_reference_written_snapshot(golden_dir):
+    ref_root = os.path.join(golden_dir, "c1_simple", "snapshot")
+    inputs = torch.load(os.path.join(golden_dir, "c1_simple", "inputs.pt"), weights_only=False)
+    app_state = _c1_app_state(seed=99)  # different weights, same structure
+    Snapshot(ref_root).restore(app_state)
+    sd = app_state["model"].state_dict()
+    for name, t in sd.items():
+        assert oracle.serialize(t) == oracle.serialize(inputs["tensors"][f"model/{name}"])
+    osd = app_state["optim"].state_dict()
+    assert oracle.serialize(osd["state"][0]["exp_avg"]) == oracle.serialize(inputs["tensors"]["optim/state/0/exp_avg"])
+    assert osd["param_groups"][0]["betas"] == (0.9, 0.999) and osd["param_groups"][0]["lr"] == 1e-3
+    assert app_state["progress"]["current_epoch"] == 0
+    # random access
+    snap = Snapshot(ref_root)
+    w = snap.read_object("0/model/0.weight")
+    assert oracle.serialize(w) == oracle.serialize(inputs["tensors"]["model/0.weight"])
+    assert snap.read_object("0/progress/current_epoch") == 0
+    out = torch.zeros(64, 128)
+    assert snap.read_object("0/model/0.weight", obj_out=out, memory_budget_bytes=4096) is not None
+    assert oracle.serialize(out) == oracle.serialize(inputs["tensors"]["model/0.weight"])
+    with pytest.raises(RuntimeError):
+        snap.read_object("0/nope")
+
+
+@pytest.mark.parametrize("batching", [True, False])
+def test_round_trip_with_odd_structures(tmp_path, batching):
+    state = StateDict(
+        {
+            "a/b": torch.arange(10, dtype=torch.int16),
+            "%weird": [torch.randn(3, 3), {"x": torch.randn(2).bfloat16(), 7: torch.tensor(True)}],
+            "od": OrderedDict(z=1, y=2.5, s="str", b=b"bytes", t=(1, 2)),
+            "c": torch.randn(4, 4, dtype=torch.complex64),
+            "nc": torch.randn(6, 8)[:, ::2],
+            "scalar": torch.tensor(3.5, dtype=torch.float64),
+            "collide": {1: "a", "1": "b"},
+        }
+    )
+    path = str(tmp_path / "s")
+    with knobs.override_is_batching_disabled(not batching):
+        snap = Snapshot.take(path, {"st": state, "rng": RNGState()})
+    rng_after_take = torch.get_rng_state()
+    meta = SnapshotMetadata.from_yaml(open(os.path.join(path, ".snapshot_metadata")).read())
+    assert meta.manifest["0/st/od/y"].type == "float" and meta.manifest["0/st/od/y"].get_value() == 2.5
+    assert meta.manifest["0/st/collide"].type == "object"
+    if batching:
+        assert meta.manifest["0/st/a%2Fb"].location.startswith("batched/")
+    else:
+        assert meta.manifest["0/st/a%2Fb"].location == "0/st/a%2Fb"
+    out = StateDict(
+        {
+            "a/b": torch.zeros(10, dtype=torch.int16),
+            "%weird": [torch.zeros(3, 3), {"x": torch.zeros(2).bfloat16(), 7: torch.tensor(False)}],
+            "od": OrderedDict(),
+            "c": torch.zeros(4, 4, dtype=torch.complex64),
+            "nc": torch.zeros(6, 4),
+            "scalar": torch.tensor(0.0, dtype=torch.float64),
+            "collide": None,
+        }
+    )
+    torch.manual_seed(1)
+    snap.restore({"st": out, "rng": RNGState()})
+    assert torch.equal(torch.get_rng_state(), rng_after_take)
+    assert torch.equal(out["a/b"], state["a/b"]) and torch.equal(out["%weird"][0], state["%weird"][0])
+    assert torch.equal(out["%weird"][1]["x"], state["%weird"][1]["x"]) and bool(out["%weird"][1][7]) is True
+    assert out["od"] == state["od"] and isinstance(out["od"], OrderedDict)
+    assert torch.equal(out["c"], state["c"]) and torch.equal(out["nc"], state["nc"].contiguous())
+    assert out["scalar"].item() == 3.5 and out["collide"] == {1: "a", "1": "b"}
+
+
+def test_large_tensor_is_chunked_and_restored(tmp_path):
+    t = torch.randn(64, 33)
+    with knobs.override_max_chunk_size_bytes(1000), knobs.override_slab_size_threshold_bytes(600):
+        snap = Snapshot.take(str(tmp_path / "s"), {"st": StateDict(t=t)})
+    e = snap.get_manifest()["0/st/t"]
+    # ceil(8448 / 1000) = 9 requested chunks -> 8 rows each -> torch.chunk semantics give 8 chunks
+    assert e.type == "ChunkedTensor" and len(e.chunks) == 8
+    assert [c.tensor.location for c in e.chunks] == [f"0/st/t_{8 * i}_0" for i in range(8)]
+    out = StateDict(t=torch.zeros(64, 33))
+    snap.restore({"st": out})
+    assert torch.equal(out["t"], t)
+
+
+def test_async_take_commits_metadata_last_and_surfaces_errors(tmp_path, monkeypatch):
+    from torchsnapshot_b200.storage_plugins import fs as fsmod
+
+    state = StateDict(t=torch.randn(100, 100), u=torch.arange(7))
+    pending = Snapshot.async_take(str(tmp_path / "ok"), {"st": state})
+    state["t"].zero_()  # mutation after async_take returns must not leak into the snapshot
+    snap = pending.wait()
+    assert pending.done()
+    out = StateDict(t=torch.zeros(100, 100), u=torch.zeros(7, dtype=torch.int64))
+    snap.restore({"st": out})
+    assert out["t"].abs().sum() > 0 and torch.equal(out["u"], torch.arange(7))
+
+    class Faulty(fsmod.FSStoragePlugin):
+        async def write(self, write_io):
+            raise OSError("disk on fire")
+
+    import torchsnapshot_b200.storage_plugin as sp
+
+    monkeypatch.setattr(sp, "FSStoragePlugin", Faulty)
+    pending = Snapshot.async_take(str(tmp_path / "bad"), {"st": StateDict(t=torch.randn(10))})
+    with pytest.raises(OSError, match="disk on fire"):
+        pending.wait()
+    assert not os.path.exists(str(tmp_path / "bad" / ".snapshot_metadata"))
+
+
+def test_edge_cases_the_reference_cannot_stage(tmp_path):
+    """Empty tensors and bf16 tensors with an odd element count (the reference drops bytes or
+    raises there: SURVEY 8a quirk 1, serialization.py:188)."""
+    state = StateDict(empty=torch.zeros(0, 3), bf_odd=torch.randn(5).bfloat16(), bf_scalar=torch.tensor(1.5).bfloat16(),
+                      after=torch.arange(3, dtype=torch.int32))
+    snap = Snapshot.take(str(tmp_path / "s"), {"st": state})
+    m = snap.get_manifest()
+    assert m["0/st/bf_odd"].byte_range[1] - m["0/st/bf_odd"].byte_range[0] == 10
+    out = StateDict(empty=torch.ones(0, 3), bf_odd=torch.zeros(5).bfloat16(), bf_scalar=torch.tensor(0.0).bfloat16(),
+                    after=torch.zeros(3, dtype=torch.int32))
+    snap.restore({"st": out})
+    assert torch.equal(out["bf_odd"], state["bf_odd"]) and out["bf_scalar"].item() == 1.5
+    assert torch.equal(out["after"], state["after"]) and out["empty"].shape == (0, 3)

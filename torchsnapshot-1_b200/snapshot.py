@@ -1,0 +1,500 @@
+"""Snapshot.take / async_take / restore / read_object over the B200 hot path.
+
+The public surface and the on-disk result are the reference's (torchsnapshot/snapshot.py:66-947):
+same arguments, same `.snapshot_metadata` document, same file layout (`<rank>/...`,
+`replicated/...`, `sharded/...`, `batched/<uuid>`), same commit rule (payload first, metadata last,
+written by rank 0 after every rank has finished).  This module is deliberately thin -- it is the
+caller of the hot path, kept only so the path can be driven and measured end to end without the
+reference installed; the planning and byte movement live in io_preparer / batcher / scheduler.
+
+Fewer metadata collectives than the reference (3 object all-gathers per take instead of ~12,
+SURVEY 2.3): path + replication globs + keys + hostname travel in one, the replicated-path
+verification and the write partitioning in a second, the manifest in a third.
+"""
+
+import asyncio
+import fnmatch
+import functools
+import itertools
+import logging
+import os
+import socket
+import sys
+import threading
+import time
+from collections import defaultdict
+from typing import Any, Callable, Dict, List, Optional, Set, Tuple
+
+import torch
+
+from . import knobs
+from .batcher import batch_read_requests, batch_write_requests
+from .flatten import _encode, flatten, inflate
+from .io_preparer import _is_sharded_tensor, prepare_read, prepare_write
+from .io_types import ReadIO, ReadReq, StoragePlugin, WriteIO, WriteReq
+from .manifest import (
+    Entry,
+    Manifest,
+    PrimitiveEntry,
+    ShardedTensorEntry,
+    SnapshotMetadata,
+    is_container_entry,
+    is_replicated,
+)
+from .partitioner import consolidate_replicated_entries, partition_write_reqs
+from .pg_wrapper import PGWrapper
+from .scheduler import (
+    PendingIOWork,
+    _MAX_PER_RANK_MEMORY_BUDGET_BYTES,
+    get_process_memory_budget_bytes,
+    sync_execute_read_reqs,
+    sync_execute_write_reqs,
+)
+from .storage_plugin import url_to_storage_plugin
+
+logger: logging.Logger = logging.getLogger(__name__)
+
+SNAPSHOT_METADATA_FNAME = ".snapshot_metadata"
+VERSION = "0.1.0"  # the metadata schema version the reference writes (torchsnapshot/version.py:17)
+
+AppState = Dict[str, Any]
+
+
+class StateDict(dict):
+    """dict that is its own state dict (reference state_dict.py:13-41)."""
+
+    def state_dict(self) -> Dict[str, Any]:
+        return dict(self)
+
+    def load_state_dict(self, state_dict: Dict[str, Any]) -> None:
+        self.clear()
+        self.update(state_dict)
+
+
+def _validate_app_state(app_state: AppState) -> None:
+    for key, value in app_state.items():
+        if not (hasattr(value, "state_dict") and hasattr(value, "load_state_dict")):
+            raise TypeError(f"Expected Stateful in app_state for key {key}, got {type(value)}.")
+
+
+def _infer_replicated(replicated: List[str], app_state: AppState) -> List[str]:
+    out = list(replicated)
+    if "**" in out:
+        return out
+    from torch.nn.parallel import DistributedDataParallel as DDP
+
+    for key, val in app_state.items():
+        if isinstance(val, DDP):
+            ignored = set(getattr(val, "parameters_to_ignore", []) or [])
+            if not ignored:
+                out.append(os.path.join(key, "**"))
+                continue
+            for name, _ in itertools.chain(val.named_parameters(), val.named_buffers()):
+                if name not in ignored:
+                    out.append(os.path.join(key, name))
+    return out
+
+
+def _memory_budget(local_world_size: int) -> int:
+    if "TORCHSNAPSHOT_PER_RANK_MEMORY_BUDGET_BYTES" in os.environ:
+        return get_process_memory_budget_bytes(None)
+    import psutil
+
+    return min(int(psutil.virtual_memory().available * 0.6) // max(local_world_size, 1), _MAX_PER_RANK_MEMORY_BUDGET_BYTES)
+
+
+class Snapshot:
+    def __init__(self, path: str, pg: Optional[Any] = None, storage_options: Optional[Dict[str, Any]] = None) -> None:
+        self.path = path
+        self.pg = pg
+        self._storage_options = storage_options
+        self._metadata: Optional[SnapshotMetadata] = None
+
+    # ------------------------------------------------------------------------------------------
+    # take
+    # ------------------------------------------------------------------------------------------
+    @classmethod
+    def take(
+        cls,
+        path: str,
+        app_state: AppState,
+        pg: Optional[Any] = None,
+        replicated: Optional[List[str]] = None,
+        storage_options: Optional[Dict[str, Any]] = None,
+        _custom_tensor_prepare_func: Optional[Callable[[str, torch.Tensor, bool], torch.Tensor]] = None,
+    ) -> "Snapshot":
+        _validate_app_state(app_state)
+        event_loop = asyncio.new_event_loop()
+        pg_wrapper = PGWrapper(pg)
+        path, pending, metadata, storage = cls._take_impl(
+            path, app_state, replicated or [], pg_wrapper, storage_options, event_loop, False,
+            _custom_tensor_prepare_func,
+        )
+        pending.sync_complete(event_loop)
+        # commit: every rank's payload is durable before rank 0 publishes the metadata
+        pg_wrapper.barrier()
+        if pg_wrapper.get_rank() == 0:
+            cls._write_snapshot_metadata(metadata, storage, event_loop)
+        storage.sync_close(event_loop=event_loop)
+        event_loop.close()
+        snapshot = cls(path=path, pg=pg, storage_options=storage_options)
+        snapshot._metadata = metadata
+        return snapshot
+
+    @classmethod
+    def async_take(
+        cls,
+        path: str,
+        app_state: AppState,
+        pg: Optional[Any] = None,
+        replicated: Optional[List[str]] = None,
+        storage_options: Optional[Dict[str, Any]] = None,
+        _custom_tensor_prepare_func: Optional[Callable[[str, torch.Tensor, bool], torch.Tensor]] = None,
+    ) -> "PendingSnapshot":
+        """Returns once a consistent copy of the state exists (packed in HBM or staged on the host);
+        D2H copies and storage I/O continue in a background thread."""
+        _validate_app_state(app_state)
+        event_loop = asyncio.new_event_loop()
+        pg_wrapper = PGWrapper(pg)
+        path, pending, metadata, storage = cls._take_impl(
+            path, app_state, replicated or [], pg_wrapper, storage_options, event_loop, True,
+            _custom_tensor_prepare_func,
+        )
+        return PendingSnapshot(path, pending, pg_wrapper, metadata, storage, event_loop, storage_options)
+
+    @classmethod
+    def _take_impl(
+        cls,
+        path: str,
+        app_state: AppState,
+        replicated: List[str],
+        pg: PGWrapper,
+        storage_options: Optional[Dict[str, Any]],
+        event_loop: asyncio.AbstractEventLoop,
+        is_async: bool,
+        prepare_func: Optional[Callable[[str, torch.Tensor, bool], torch.Tensor]],
+    ) -> Tuple[str, PendingIOWork, SnapshotMetadata, StoragePlugin]:
+        rank, world = pg.get_rank(), pg.get_world_size()
+        app_state = dict(app_state)
+        # ---- collective 1: path, replication globs, keys, host ---------------------------------
+        hello: List[Any] = [None] * world
+        pg.all_gather_object(hello, (path, _infer_replicated(replicated, app_state), list(app_state.keys()),
+                                     socket.gethostname()))
+        if hello[0][0] != path:
+            logger.warning(f"Rank {rank} specified a path ({path}) different from rank 0 ({hello[0][0]}).")
+        path = hello[0][0]
+        globs = set.intersection(*(set(h[1]) for h in hello))
+        global_keys = sorted(set(itertools.chain.from_iterable(h[2] for h in hello)))
+        local_world = sum(1 for h in hello if h[3] == hello[rank][3])
+        storage = url_to_storage_plugin(path, storage_options)
+
+        # ---- state dicts -> flat leaves (RNG state first, restored afterwards) -----------------
+        manifest: Manifest = {}
+        flattened: Dict[str, Any] = {}
+        rng_items = [(k, v) for k, v in app_state.items() if type(v).__name__ == "RNGState"]
+        if len(rng_items) > 1:
+            raise RuntimeError(f"Multiple RNGState objects in app state: {[k for k, _ in rng_items]}")
+        rng_sd = None
+        if rng_items:
+            rng_key, rng_obj = rng_items[0]
+            del app_state[rng_key]
+            rng_sd = rng_obj.state_dict()
+            m, f = flatten(rng_sd, prefix=rng_key)
+            manifest.update(m)
+            flattened.update(f)
+        for key in global_keys:
+            if key in app_state:
+                m, f = flatten(app_state[key].state_dict(), prefix=key)
+                manifest.update(m)
+                flattened.update(f)
+            if world > 1:
+                pg.barrier()  # state_dict() may run collectives; keep ranks in step
+        if rng_items:
+            rng_items[0][1].load_state_dict(rng_sd)
+
+        # ---- plan --------------------------------------------------------------------------------
+        candidates = [
+            p for p, v in flattened.items() if not _is_sharded_tensor(v) and any(fnmatch.fnmatch(p, g) for g in globs)
+        ]
+        if world > 1:
+            # ---- collective 2: which candidate paths exist on every rank ----------------------
+            seen: List[Any] = [None] * world
+            pg.all_gather_object(seen, candidates)
+            counts: Dict[str, int] = defaultdict(int)
+            for paths in seen:
+                for p in paths:
+                    counts[p] += 1
+            replicated_paths = {p for p in seen[0] if counts[p] == world}
+        else:
+            replicated_paths = set(candidates)
+
+        object_entries: Dict[str, Entry] = {}
+        write_reqs_by_path: Dict[str, List[WriteReq]] = {}
+        primitive_entries: Dict[str, Entry] = {}
+        for logical_path, obj in flattened.items():
+            entry, wrs = prepare_write(
+                obj=obj,
+                logical_path=logical_path,
+                rank=rank,
+                replicated=logical_path in replicated_paths,
+                is_async_snapshot=is_async,
+                _tensor_prepare_func=functools.partial(prepare_func, logical_path) if prepare_func else None,
+            )
+            if isinstance(entry, PrimitiveEntry):
+                primitive_entries[logical_path] = entry
+            else:
+                object_entries[logical_path] = entry
+                write_reqs_by_path[logical_path] = wrs
+        object_entries, write_reqs_by_path = partition_write_reqs(object_entries, write_reqs_by_path, pg)
+        write_reqs = [wr for wrs in write_reqs_by_path.values() for wr in wrs]
+        if not knobs.is_batching_disabled():
+            _, write_reqs = batch_write_requests(entries=list(object_entries.values()), write_reqs=write_reqs)
+        manifest.update(primitive_entries)
+        manifest.update(object_entries)
+
+        # ---- collective 3: the manifest ----------------------------------------------------------
+        manifests: List[Any] = [None] * world
+        pg.all_gather_object(manifests, manifest)
+        manifests = consolidate_replicated_entries(manifests)
+        global_manifest: Manifest = {}
+        for r, m in enumerate(manifests):
+            for logical_path, entry in m.items():
+                global_manifest[os.path.join(str(r), logical_path)] = entry
+
+        pending = sync_execute_write_reqs(
+            write_reqs=write_reqs,
+            storage=storage,
+            memory_budget_bytes=_memory_budget(local_world),
+            rank=rank,
+            event_loop=event_loop,
+        )
+        metadata = SnapshotMetadata(version=VERSION, world_size=world, manifest=global_manifest)
+        return path, pending, metadata, storage
+
+    # ------------------------------------------------------------------------------------------
+    # restore / read_object
+    # ------------------------------------------------------------------------------------------
+    def restore(self, app_state: AppState) -> None:
+        _validate_app_state(app_state)
+        event_loop = asyncio.new_event_loop()
+        pg = PGWrapper(self.pg)
+        rank, world = pg.get_rank(), pg.get_world_size()
+        storage = url_to_storage_plugin(self.path, self._storage_options)
+        app_state = dict(app_state)
+        rng_items = [(k, v) for k, v in app_state.items() if type(v).__name__ == "RNGState"]
+        keys: List[Any] = [None] * world
+        pg.all_gather_object(keys, (list(app_state.keys()), socket.gethostname()))
+        global_keys = sorted(set(itertools.chain.from_iterable(k[0] for k in keys)))
+        local_world = sum(1 for k in keys if k[1] == keys[rank][1])
+        budget = _memory_budget(local_world)
+        rng_key = rng_items[0][0] if rng_items else None
+        for key in global_keys:
+            if key != rng_key:
+                self._load_stateful(key, app_state.get(key), storage, rank, budget, event_loop)
+            if world > 1:
+                pg.barrier()
+        if rng_key is not None:  # RNG state last, so loading has no side effect on it
+            self._load_stateful(rng_key, app_state[rng_key], storage, rank, budget, event_loop)
+        storage.sync_close(event_loop=event_loop)
+        event_loop.close()
+
+    def _load_stateful(
+        self, key: str, stateful: Optional[Any], storage: StoragePlugin, rank: int, budget: int,
+        event_loop: asyncio.AbstractEventLoop,
+    ) -> None:
+        if stateful is None:
+            return
+        manifest, merged_sd = get_manifest_for_rank(self.metadata, rank)
+        # load straight into the tensors the stateful already owns (no second copy of the state)
+        _, flattened = flatten(stateful.state_dict(), prefix=key)
+        flattened = {k: v for k, v in flattened.items() if isinstance(v, torch.Tensor) or _is_sharded_tensor(v)}
+        # a rank that did not exist at save time still gets the sharded entries it asks for
+        for logical_path in flattened:
+            if logical_path not in manifest and logical_path in merged_sd:
+                manifest[logical_path] = merged_sd[logical_path]
+        prefix = _encode(key)
+        containers: Manifest = {}
+        read_reqs: List[ReadReq] = []
+        futs: Dict[str, Any] = {}
+        for logical_path, entry in manifest.items():
+            if logical_path.split("/")[0] != prefix:
+                continue
+            if is_container_entry(entry):
+                containers[logical_path] = entry
+                continue
+            if isinstance(entry, ShardedTensorEntry) and logical_path not in flattened:
+                continue  # sharded entries can only be loaded into a runtime object
+            rrs, fut = prepare_read(entry=entry, obj_out=flattened.get(logical_path))
+            read_reqs += rrs
+            futs[logical_path] = fut
+            flattened.pop(logical_path, None)
+        if not knobs.is_batching_disabled():
+            read_reqs = batch_read_requests(read_reqs=read_reqs)
+        sync_execute_read_reqs(
+            read_reqs=read_reqs, storage=storage, memory_budget_bytes=budget, rank=rank, event_loop=event_loop
+        )
+        state_dict = inflate(containers, {k: fut.obj for k, fut in futs.items()}, prefix=key)
+        stateful.load_state_dict(state_dict)
+
+    def read_object(self, path: str, obj_out: Optional[Any] = None, memory_budget_bytes: Optional[int] = None) -> Any:
+        """Random access to one persisted object, `path` = "<rank>/<logical path>"; no collectives
+        (reference snapshot.py:501-594)."""
+        rank_str, _, logical_path = path.partition("/")
+        try:
+            rank = int(rank_str)
+        except ValueError:
+            raise RuntimeError(f'The path must be in the form "RANK/LOGICAL_PATH" (got {path}).') from None
+        manifest, merged_sd = get_manifest_for_rank(self.metadata, rank)
+        entry = merged_sd.get(logical_path) or manifest.get(logical_path)
+        if entry is None:
+            raise RuntimeError(f'The supplied path "{path}" does not exist in the snapshot\'s manifest.')
+        if isinstance(entry, PrimitiveEntry):
+            return entry.get_value()
+        read_reqs, fut = prepare_read(entry=entry, obj_out=obj_out, buffer_size_limit_bytes=memory_budget_bytes)
+        if not knobs.is_batching_disabled():
+            read_reqs = batch_read_requests(read_reqs=read_reqs)
+        event_loop = asyncio.new_event_loop()
+        storage = url_to_storage_plugin(self.path, self._storage_options)
+        sync_execute_read_reqs(
+            read_reqs=read_reqs,
+            storage=storage,
+            memory_budget_bytes=memory_budget_bytes or _MAX_PER_RANK_MEMORY_BUDGET_BYTES,
+            rank=0,
+            event_loop=event_loop,
+        )
+        storage.sync_close(event_loop=event_loop)
+        event_loop.close()
+        return fut.obj
+
+    # ------------------------------------------------------------------------------------------
+    # metadata
+    # ------------------------------------------------------------------------------------------
+    @property
+    def metadata(self) -> SnapshotMetadata:
+        if self._metadata is None:
+            event_loop = asyncio.new_event_loop()
+            storage = url_to_storage_plugin(self.path, self._storage_options)
+            read_io = ReadIO(path=SNAPSHOT_METADATA_FNAME)
+            storage.sync_read(read_io=read_io, event_loop=event_loop)
+            self._metadata = SnapshotMetadata.from_yaml(read_io.buf.getvalue().decode("utf-8"))
+            storage.sync_close(event_loop=event_loop)
+            event_loop.close()
+        return self._metadata
+
+    def get_manifest(self) -> Dict[str, Entry]:
+        import copy
+
+        return copy.deepcopy(self.metadata.manifest)
+
+    @staticmethod
+    def _write_snapshot_metadata(
+        metadata: SnapshotMetadata, storage: StoragePlugin, event_loop: asyncio.AbstractEventLoop
+    ) -> None:
+        storage.sync_write(
+            WriteIO(path=SNAPSHOT_METADATA_FNAME, buf=metadata.to_yaml().encode("utf-8")), event_loop=event_loop
+        )
+
+
+def get_manifest_for_rank(metadata: SnapshotMetadata, rank: int) -> Tuple[Manifest, Dict[str, ShardedTensorEntry]]:
+    """The view of the global manifest a rank restores from (reference manifest_ops.py:24-115):
+    its own entries plus the replicated ones (listed under rank 0); sharded entries merged over all
+    ranks; a rank that did not exist at save time sees the replicated entries only."""
+    per_rank: List[Manifest] = [{} for _ in range(metadata.world_size)]
+    for path, entry in metadata.manifest.items():
+        r, _, logical_path = path.partition("/")
+        per_rank[int(r)][logical_path] = entry
+    shards_by_path: Dict[str, List[Any]] = defaultdict(list)
+    for m in per_rank:
+        for logical_path, entry in m.items():
+            if isinstance(entry, ShardedTensorEntry):
+                shards_by_path[logical_path] += entry.shards
+    merged = {
+        p: ShardedTensorEntry(shards=sorted(shards, key=lambda s: s.offsets)) for p, shards in shards_by_path.items()
+    }
+    if rank < metadata.world_size:
+        local = dict(per_rank[rank])
+        for logical_path, entry in per_rank[0].items():
+            if is_replicated(entry):
+                local[logical_path] = entry
+        for logical_path, entry in list(local.items()):
+            if isinstance(entry, ShardedTensorEntry):
+                local[logical_path] = merged[logical_path]
+    else:
+        local = {p: e for p, e in per_rank[0].items() if is_container_entry(e) or is_replicated(e)}
+    return local, merged
+
+
+class PendingSnapshot:
+    """Handle of an async_take: the background thread finishes D2H + storage I/O, then the ranks
+    agree (through the default store, never through collectives in this thread) and rank 0
+    commits the metadata (reference snapshot.py:856-947)."""
+
+    DEFAULT_BARRIER_TIMEOUT_S = 1800
+    _seq = 0
+
+    def __init__(
+        self,
+        path: str,
+        pending_io_work: PendingIOWork,
+        pg: PGWrapper,
+        metadata: SnapshotMetadata,
+        storage: StoragePlugin,
+        event_loop: asyncio.AbstractEventLoop,
+        storage_options: Optional[Dict[str, Any]],
+    ) -> None:
+        self.path = path
+        self.pg_obj = pg.pg
+        self._storage_options = storage_options
+        self.exc_info: Optional[Any] = None
+        self._done = False
+        self._rank, self._world = pg.get_rank(), pg.get_world_size()
+        self._store = None
+        if self._world > 1:
+            import torch.distributed as dist
+
+            self._store = dist.distributed_c10d._get_default_store()
+        PendingSnapshot._seq += 1  # every rank takes the same sequence of async snapshots
+        self._key = f"tsb200_{path}_{PendingSnapshot._seq}"
+        self.thread = threading.Thread(
+            target=self._complete, args=(pending_io_work, metadata, storage, event_loop), daemon=True
+        )
+        self.thread.start()
+
+    def _complete(self, pending: PendingIOWork, metadata: SnapshotMetadata, storage: StoragePlugin,
+                  event_loop: asyncio.AbstractEventLoop) -> None:
+        err: Optional[str] = None
+        try:
+            pending.sync_complete(event_loop)
+        except BaseException as e:  # noqa: B902
+            self.exc_info = sys.exc_info()
+            err = repr(e)
+        try:
+            if self._store is not None:
+                # two-phase barrier through the store; a failed rank poisons the commit
+                self._store.set(f"{self._key}/arrive/{self._rank}", err or "ok")
+                if self._rank == 0:
+                    states = [self._store.get(f"{self._key}/arrive/{r}").decode() for r in range(self._world)]
+                    bad = [s for s in states if s != "ok"]
+                    if not bad:
+                        Snapshot._write_snapshot_metadata(metadata, storage, event_loop)
+                    self._store.set(f"{self._key}/commit", "ok" if not bad else "; ".join(bad))
+                verdict = self._store.get(f"{self._key}/commit").decode()
+                if verdict != "ok" and self.exc_info is None:
+                    raise RuntimeError(f"async snapshot failed on a peer rank: {verdict}")
+            elif err is None:
+                Snapshot._write_snapshot_metadata(metadata, storage, event_loop)
+            storage.sync_close(event_loop=event_loop)
+        except BaseException:  # noqa: B902
+            if self.exc_info is None:
+                self.exc_info = sys.exc_info()
+        finally:
+            self._done = True
+
+    def wait(self) -> Snapshot:
+        self.thread.join()
+        if self.exc_info is not None:
+            raise self.exc_info[1].with_traceback(self.exc_info[2])
+        return Snapshot(path=self.path, pg=self.pg_obj, storage_options=self._storage_options)
+
+    def done(self) -> bool:
+        return self._done
