@@ -99,6 +99,14 @@ int tsb_ctx_destroy(TsbCtx* ctx);
 int tsb_ctx_device(TsbCtx* ctx, int* device);
 /* Multiprocessor count of the context's device. */
 int tsb_ctx_sm_count(TsbCtx* ctx, int* sms);
+/*
+ * Monotonic counters since context creation (any pointer may be NULL): kernels launched by
+ * tsb_copy_regions (tile expansion + flat + strided), tsb_copy_regions calls that launched work,
+ * descriptor bytes uploaded host->device, and payload bytes the kernels were asked to move.
+ * No reference counterpart (bench.py reports them as gpu_launches / h2d bytes).
+ */
+int tsb_ctx_counters(TsbCtx* ctx, uint64_t* kernel_launches, uint64_t* copy_calls, uint64_t* desc_upload_bytes,
+                     uint64_t* kernel_payload_bytes);
 
 /* ---- arenas ------------------------------------------------------------------------ */
 

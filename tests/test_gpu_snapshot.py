@@ -223,7 +223,7 @@ def test_non_batched_large_tensors_and_chunks(tmp_path):
     g = torch.Generator(device="cuda").manual_seed(2)
     big = torch.randn(1000, 999, device="cuda", generator=g)          # > slab threshold below: written on its own
     huge = torch.randn(4000, 1000, device="cuda", generator=g)         # > chunk size below: chunked
-    view = torch.randn(3000, 1200, device="cuda", generator=g)[:, 100:1100]  # strided and unbatched
+    view = torch.randn(1200, 1200, device="cuda", generator=g)[:, 100:1100]  # strided and unbatched
     state = StateDict(big=big, huge=huge, view=view, small=torch.arange(5, device="cuda"))
     with knobs.override_slab_size_threshold_bytes(1 << 20), knobs.override_max_chunk_size_bytes(6 << 20):
         snap = Snapshot.take(str(tmp_path / "s"), {"st": state})
@@ -231,7 +231,7 @@ def test_non_batched_large_tensors_and_chunks(tmp_path):
         assert m["0/st/big"].location == "0/st/big" and m["0/st/huge"].type == "ChunkedTensor"
         assert open(os.path.join(str(tmp_path / "s"), "0/st/big"), "rb").read() == _bytes(big)
         assert open(os.path.join(str(tmp_path / "s"), "0/st/view"), "rb").read() == _bytes(view)
-        out = StateDict(big=torch.zeros_like(big), huge=torch.zeros_like(huge), view=torch.zeros(3000, 1000, device="cuda"),
+        out = StateDict(big=torch.zeros_like(big), huge=torch.zeros_like(huge), view=torch.zeros(1200, 1000, device="cuda"),
                         small=torch.zeros(5, dtype=torch.int64, device="cuda"))
         snap.restore({"st": out})
     for k in state:

@@ -160,3 +160,32 @@ def test_c1_snapshot_payloads(golden_dir):
     assert len(locations) == 1
     with open(os.path.join(root, "snapshot", locations.pop()), "rb") as f:
         assert f.read() == blob
+
+
+def test_cpu_port_of_take_and_restore(golden_dir, tmp_path):
+    """oracle/ref_path.py (the timed CPU baseline) writes the bytes the reference wrote and reads them back."""
+    from oracle import ref_path
+
+    root = os.path.join(golden_dir, "c1_simple")
+    inputs = torch.load(os.path.join(root, "inputs.pt"), weights_only=False)
+    tensors = {p: inputs["tensors"][p] for p in inputs["order"] if p in inputs["tensors"]}
+    manifest = ref_path.take(str(tmp_path / "s"), tensors)
+    ref_meta = json.load(open(os.path.join(root, "snapshot", ".snapshot_metadata")))["manifest"]
+    for path, e in manifest.items():
+        r = ref_meta[path]
+        assert e["byte_range"] == r["byte_range"] and e["dtype"] == r["dtype"] and e["shape"] == r["shape"]
+        with open(os.path.join(root, "snapshot", r["location"]), "rb") as f:
+            want = f.read()[r["byte_range"][0] : r["byte_range"][1]]
+        with open(os.path.join(str(tmp_path / "s"), e["location"]), "rb") as f:
+            assert f.read()[e["byte_range"][0] : e["byte_range"][1]] == want
+    outs = {p: torch.zeros_like(t) for p, t in tensors.items()}
+    ref_path.restore(os.path.join(root, "snapshot"), outs)  # reads the reference-written snapshot
+    for p, t in tensors.items():
+        assert oracle.serialize(outs[p]) == oracle.serialize(t)
+    big = {"a": _cases.raw_tensor(1, [300, 7], torch.bfloat16), "b": _cases.raw_tensor(2, [5000], torch.float32),
+           "c": _cases.raw_tensor(3, [64, 64], torch.float64)[:, ::2]}
+    ref_path.take(str(tmp_path / "t"), big, threshold=4096)
+    outs = {p: torch.zeros_like(t.contiguous()) for p, t in big.items()}
+    ref_path.restore(str(tmp_path / "t"), outs)
+    for p, t in big.items():
+        assert oracle.serialize(outs[p]) == oracle.serialize(t)

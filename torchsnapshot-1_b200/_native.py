@@ -55,6 +55,7 @@ _SIGNATURES = {
     "tsb_ctx_destroy": (_i, [_p]),
     "tsb_ctx_device": (_i, [_p, ctypes.POINTER(_i)]),
     "tsb_ctx_sm_count": (_i, [_p, ctypes.POINTER(_i)]),
+    "tsb_ctx_counters": (_i, [_p, ctypes.POINTER(_u64), ctypes.POINTER(_u64), ctypes.POINTER(_u64), ctypes.POINTER(_u64)]),
     "tsb_dev_alloc": (_i, [_p, _u64, ctypes.POINTER(_u64)]),
     "tsb_dev_free": (_i, [_p, _u64]),
     "tsb_host_alloc": (_i, [_p, _u64, ctypes.POINTER(_p)]),
@@ -148,6 +149,12 @@ class Context:
         if self._h is not None and self._h.value:
             self.lib.tsb_ctx_destroy(self._h)
             self._h = None
+
+    def counters(self) -> dict:
+        a, b, c, d = _u64(), _u64(), _u64(), _u64()
+        _check(self.lib, self.lib.tsb_ctx_counters(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c), ctypes.byref(d)))
+        return {"kernel_launches": a.value, "copy_calls": b.value, "desc_upload_bytes": c.value,
+                "kernel_payload_bytes": d.value}
 
     # -- arenas
     def dev_alloc(self, nbytes: int) -> int:

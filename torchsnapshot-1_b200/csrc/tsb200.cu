@@ -224,6 +224,11 @@ struct TsbCtx {
   std::vector<uint32_t> free_events;
   std::vector<PendingScratch> pending;
   std::vector<cudaEvent_t> spare_scratch_events;
+  // counters (tsb_ctx_counters)
+  uint64_t n_kernel_launches = 0;  // expand + flat + strided kernels
+  uint64_t n_copy_calls = 0;       // tsb_copy_regions calls that launched something
+  uint64_t desc_upload_bytes = 0;  // descriptor bytes copied host -> device
+  uint64_t kernel_payload_bytes = 0;
 };
 
 struct DeviceGuard {
@@ -315,6 +320,7 @@ static void flat_run(uint64_t src, uint64_t dst, uint64_t n, std::vector<TsbRun>
 struct TilePlan {
   std::vector<TsbRun> flat_runs;
   uint64_t flat_tiles = 0;
+  uint64_t payload = 0;
   std::vector<TsbTile> strided;
   std::vector<TsbRegion> strided_regions;
 };
@@ -327,6 +333,7 @@ static int build_tiles(const TsbRegion* regions, uint32_t n, TilePlan& plan) {
     uint64_t total;
     if (!region_payload(r, &total)) return set_err(TSB_EINVAL, "region %u: size overflow", i);
     if (total == 0) continue;
+    plan.payload += total;
     if (r.ndim == 0) {
       flat_run(r.src, r.dst, r.run_bytes, plan.flat_runs, &plan.flat_tiles);
       continue;
@@ -438,6 +445,17 @@ int tsb_ctx_device(TsbCtx* ctx, int* device) {
 int tsb_ctx_sm_count(TsbCtx* ctx, int* sms) {
   if (!ctx || !sms) return set_err(TSB_EINVAL, "null argument");
   *sms = ctx->sm_count;
+  return TSB_OK;
+}
+
+int tsb_ctx_counters(TsbCtx* ctx, uint64_t* kernel_launches, uint64_t* copy_calls, uint64_t* desc_upload_bytes,
+                     uint64_t* kernel_payload_bytes) {
+  if (!ctx) return set_err(TSB_EINVAL, "null context");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  if (kernel_launches) *kernel_launches = ctx->n_kernel_launches;
+  if (copy_calls) *copy_calls = ctx->n_copy_calls;
+  if (desc_upload_bytes) *desc_upload_bytes = ctx->desc_upload_bytes;
+  if (kernel_payload_bytes) *kernel_payload_bytes = ctx->kernel_payload_bytes;
   return TSB_OK;
 }
 
@@ -656,6 +674,13 @@ static int copy_regions_impl(TsbCtx* ctx, int stream, const TsbRegion* regions, 
     e = cudaGetLastError();
   }
   if (kernel_stop && event_lookup(ctx, *kernel_stop, &ev_stop) == TSB_OK) cudaEventRecord(ev_stop, s);
+  {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    ctx->n_copy_calls += 1;
+    ctx->n_kernel_launches += (plan.flat_tiles ? 2 : 0) + (plan.strided.empty() ? 0 : 1);
+    ctx->desc_upload_bytes += upload;
+    ctx->kernel_payload_bytes += plan.payload;
+  }
   // the scratch is released once the launch has completed
   PendingScratch p;
   p.hbuf = hbuf;

@@ -35,6 +35,7 @@ import psutil
 from . import _native
 from ._native import ArenaFull, STREAM_D2H, STREAM_H2D, STREAM_PACK
 from .engine import Engine, PinnedBuffer, get_engine, readonly_buffer_address
+from .regions import regions_to_array
 from .io_types import BufferType, ReadIO, ReadReq, StoragePlugin, WriteIO, WriteReq
 
 logger: logging.Logger = logging.getLogger(__name__)
@@ -100,6 +101,15 @@ class _Stats:
         # device-timed bracket of the take: first pack launch -> last D2H complete
         self.pack_events: List[Tuple[Engine, int, int, int]] = []  # (engine, start, stop, kernel bytes)
         self.d2h_end_events: List[Tuple[Engine, int]] = []
+        # events around the copy kernels only (descriptor upload / tile expansion excluded)
+        self.kernel_events: List[Tuple[Engine, int, int, int]] = []
+
+    def kernel_ms(self) -> float:
+        return sum(eng.ctx.event_elapsed_ms(a, b) for eng, a, b, _n in self.kernel_events)
+
+    def kernel_bytes(self) -> int:
+        """Algorithmic HBM bytes of the pack launches: 2 x packed payload (read + write)."""
+        return sum(n for _e, _a, _b, n in self.kernel_events)
 
     def pack_ms(self) -> float:
         """Device time of the pack launches (CUDA events on the pack stream)."""
@@ -123,11 +133,27 @@ class _Stats:
             eng.ctx.event_release(b)
         for eng, e in self.d2h_end_events:
             eng.ctx.event_release(e)
+        for eng, a, b, _n in self.kernel_events:
+            eng.ctx.event_release(a)
+            eng.ctx.event_release(b)
         self.pack_events = []
         self.d2h_end_events = []
+        self.kernel_events = []
 
 
 last_write_stats: Optional[_Stats] = None  # introspection hook for bench.py
+
+
+class _ReadStats:
+    def __init__(self) -> None:
+        self.begin = time.monotonic()
+        self.bytes = 0
+        self.device_bytes = 0  # bytes that went pinned -> H2D -> unpack kernel
+        self.unpack_ms = 0.0  # device time of the unpack kernels (CUDA events)
+        self.unpack_launches = 0
+
+
+last_read_stats: Optional[_ReadStats] = None
 
 
 async def _wait_event(loop: asyncio.AbstractEventLoop, executor: Optional[Executor], eng: Engine, ev: int) -> None:
@@ -317,7 +343,10 @@ async def execute_write_reqs(
                 eng.wait_current_stream(STREAM_PACK)
                 first = False
             ev_start = ctx.event_record(STREAM_PACK)
-            eng.copy_regions(regions, STREAM_PACK)
+            arr = regions_to_array(regions)
+            if arr.shape[0]:
+                k0, k1 = eng.copy_region_array_timed(arr, STREAM_PACK)
+                stats.kernel_events.append((eng, k0, k1, 2 * sum(n for _p, _o, n in files)))
             ev_pack = ctx.event_record(STREAM_PACK)
             stats.pack_events.append((eng, ev_start, ev_pack, 2 * sum(n for _p, _o, n in files)))
             pack_waits.append((eng, ev_pack))
@@ -406,6 +435,9 @@ async def execute_read_reqs(
     executor = ThreadPoolExecutor(max_workers=_MAX_PER_RANK_CPU_CONCURRENCY, thread_name_prefix="tsb-consume")
     io_slots = asyncio.Semaphore(_MAX_PER_RANK_IO_CONCURRENCY)
     alloc = _Allocator()
+    global last_read_stats
+    rstats = _ReadStats()
+    last_read_stats = rstats
     begin = time.monotonic()
     bytes_read = 0
     ordered: Set[int] = set()
@@ -431,12 +463,21 @@ async def execute_read_reqs(
                     ev_h2d = ctx.event_record(STREAM_H2D)
                     ctx.stream_wait_event(STREAM_PACK, ev_h2d)
                     ctx.event_release(ev_h2d)
-                    eng.copy_regions(consumer.unpack_regions(dptr), STREAM_PACK)
+                    arr = regions_to_array(consumer.unpack_regions(dptr))
+                    k0 = k1 = None
+                    if arr.shape[0]:
+                        k0, k1 = eng.copy_region_array_timed(arr, STREAM_PACK)
                     ev = ctx.event_record(STREAM_PACK)
                     try:
                         await _wait_event(loop, executor, eng, ev)
+                        if k0 is not None:
+                            rstats.unpack_ms += ctx.event_elapsed_ms(k0, k1)
+                            rstats.unpack_launches += 1
                     finally:
                         ctx.event_release(ev)
+                        if k0 is not None:
+                            ctx.event_release(k0)
+                            ctx.event_release(k1)
                 finally:
                     ctx.dev_free(dptr)
                     alloc.notify()
@@ -444,6 +485,7 @@ async def execute_read_reqs(
                 pbuf.release()
                 alloc.notify()
         bytes_read += nbytes
+        rstats.device_bytes += nbytes
 
     budget = memory_budget_bytes
     budget_freed = asyncio.Event()
@@ -488,6 +530,7 @@ async def execute_read_reqs(
         raise
     finally:
         executor.shutdown(wait=False)
+    rstats.bytes = bytes_read
     elapsed = max(time.monotonic() - begin, 1e-9)
     logger.info(f"Rank {rank} finished loading. Throughput: {bytes_read / 1024**2 / elapsed:.2f}MB/s")
 
