@@ -334,7 +334,10 @@ def main():
                 res["step_wall"].append(max_over_ranks(time.monotonic() - s0))
     counters1 = eng.ctx.counters()
     # verify once, outside the timed region, that the restored bytes are the saved bytes
-    ok = all(torch.equal(outs[k], state[k]) for k in list(state)[:: max(len(state) // 64, 1)])
+    def same_bytes(a, b):  # bit patterns include NaNs, so compare integers, not floats
+        return torch.equal(a.reshape(-1).view(torch.uint8), b.reshape(-1).view(torch.uint8))
+
+    ok = all(same_bytes(outs[k], state[k]) for k in list(state)[:: max(len(state) // 64, 1)])
     assert ok, "restored state differs from the saved state"
 
     K = len(res["dev_ms"])

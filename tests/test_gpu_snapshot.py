@@ -13,7 +13,7 @@ import torch
 
 import _cases
 import oracle
-from test_snapshot_cpu import _c1_app_state, _normalise, _payloads
+from test_snapshot_cpu import _c1_app_state, _c1_inputs, _normalise, _payloads
 from torchsnapshot_b200 import knobs
 from torchsnapshot_b200.io_types import ReadIO, StoragePlugin, WriteIO
 from torchsnapshot_b200.snapshot import Snapshot, StateDict
@@ -43,7 +43,7 @@ def test_c1_on_gpu_matches_reference_snapshot(golden_dir, tmp_path, engine):
     """BASELINE config 0 with the state on the GPU: payload bytes and manifest equal the snapshot
     the reference wrote for the same state."""
     ref_root = os.path.join(golden_dir, "c1_simple", "snapshot")
-    app_state = _to_cuda(_c1_app_state())
+    app_state = _to_cuda(_c1_app_state(inputs=_c1_inputs(golden_dir)))
     launches = engine.launches
     ours = str(tmp_path / "snap")
     Snapshot.take(ours, app_state)

@@ -21,14 +21,27 @@ def sha(b) -> str:
     return hashlib.sha256(bytes(b)).hexdigest()
 
 
-def _c1_app_state(seed=1234, step=True):
+def _c1_app_state(seed=1234, step=True, inputs=None):
+    """simple_example.py-style app state.  With `inputs` (tests/golden/c1_simple/inputs.pt) the tensors
+    are the exact ones the reference saved -- recomputing them is not bit-reproducible across CPUs
+    (BLAS reduction order), and the comparison below is on bytes."""
     torch.manual_seed(seed)
     model = torch.nn.Sequential(torch.nn.Linear(128, 64), torch.nn.Linear(64, 32), torch.nn.Linear(32, 1))
     optim = torch.optim.Adam(model.parameters(), lr=1e-3)
     if step:
         model(torch.randn(16, 128)).sum().backward()
         optim.step()
+    if inputs is not None:
+        tensors = inputs["tensors"]
+        model.load_state_dict({k[len("model/"):]: v.clone() for k, v in tensors.items() if k.startswith("model/")})
+        for i, p in enumerate(model.parameters()):
+            for key in list(optim.state[p].keys()):
+                optim.state[p][key] = tensors[f"optim/state/{i}/{key}"].clone()
     return {"model": model, "optim": optim, "progress": StateDict(current_epoch=0)}
+
+
+def _c1_inputs(golden_dir):
+    return torch.load(os.path.join(golden_dir, "c1_simple", "inputs.pt"), weights_only=False)
 
 
 def _payloads(root):
@@ -61,7 +74,7 @@ def test_take_writes_what_the_reference_wrote(golden_dir, tmp_path):
     """Same app state -> same manifest (modulo slab uuids) and the same payload bytes per object."""
     ref_root = os.path.join(golden_dir, "c1_simple", "snapshot")
     ours = str(tmp_path / "snap")
-    Snapshot.take(ours, _c1_app_state())
+    Snapshot.take(ours, _c1_app_state(inputs=_c1_inputs(golden_dir)))
     ref_payloads, ref_meta = _payloads(ref_root)
     our_payloads, our_meta = _payloads(ours)
     assert our_payloads == ref_payloads
