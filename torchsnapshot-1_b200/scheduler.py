@@ -98,6 +98,9 @@ class _Stats:
         self.begin = time.monotonic()
         self.bytes = 0
         self.staging_done: Optional[float] = None
+        self.pack_launched: Optional[float] = None
+        self.d2h_done: Optional[float] = None
+        self.writes_done: Optional[float] = None
         # device-timed bracket of the take: first pack launch -> last D2H complete
         self.pack_events: List[Tuple[Engine, int, int, int]] = []  # (engine, start, stop, kernel bytes)
         self.d2h_end_events: List[Tuple[Engine, int]] = []
@@ -229,7 +232,8 @@ class PendingIOWork:
             raise
         finally:
             self.executor.shutdown(wait=False)
-        elapsed = max(time.monotonic() - self.stats.begin, 1e-9)
+        self.stats.writes_done = time.monotonic()
+        elapsed = max(self.stats.writes_done - self.stats.begin, 1e-9)
         logger.info(
             f"Rank {self.rank} completed writing in {elapsed:.3f} s "
             f"({self.stats.bytes / 1024**2 / elapsed:.1f} MB/s)"
@@ -310,6 +314,7 @@ async def execute_write_reqs(
             last_ev = ctx.event_record(STREAM_D2H)
             await _wait_event(loop, executor, eng, last_ev)
             stats.d2h_end_events.append((eng, last_ev))
+            stats.d2h_done = time.monotonic()
         finally:
             ctx.dev_free(base)
             alloc.notify()
@@ -350,6 +355,7 @@ async def execute_write_reqs(
             ev_pack = ctx.event_record(STREAM_PACK)
             stats.pack_events.append((eng, ev_start, ev_pack, 2 * sum(n for _p, _o, n in files)))
             pack_waits.append((eng, ev_pack))
+            stats.pack_launched = time.monotonic()
             spawn(drain_wave(eng, base, files, ev_pack))
             # give the drain a chance to queue its D2H copies before the next wave is planned
             await asyncio.sleep(0)

@@ -23,6 +23,7 @@ import sys
 import threading
 import time
 from collections import defaultdict
+from concurrent.futures import ThreadPoolExecutor
 from typing import Any, Callable, Dict, List, Optional, Set, Tuple
 
 import torch
@@ -130,11 +131,19 @@ class Snapshot:
             path, app_state, replicated or [], pg_wrapper, storage_options, event_loop, False,
             _custom_tensor_prepare_func,
         )
+        # serialise the manifest while the D2H copies and storage writes drain
+        yaml_future = None
+        if pg_wrapper.get_rank() == 0:
+            yaml_pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix="tsb-meta")
+            yaml_future = yaml_pool.submit(metadata.to_yaml)
         pending.sync_complete(event_loop)
         # commit: every rank's payload is durable before rank 0 publishes the metadata
         pg_wrapper.barrier()
-        if pg_wrapper.get_rank() == 0:
-            cls._write_snapshot_metadata(metadata, storage, event_loop)
+        if yaml_future is not None:
+            storage.sync_write(
+                WriteIO(path=SNAPSHOT_METADATA_FNAME, buf=yaml_future.result().encode("utf-8")), event_loop=event_loop
+            )
+            yaml_pool.shutdown(wait=False)
         storage.sync_close(event_loop=event_loop)
         event_loop.close()
         snapshot = cls(path=path, pg=pg, storage_options=storage_options)

@@ -23,7 +23,9 @@ class FSStoragePlugin(StoragePlugin):
         self.root = root
         self._dir_cache: Set[str] = set()
         self._executor = ThreadPoolExecutor(max_workers=16, thread_name_prefix="tsb-fs")
-        self._io_threads = knobs.get_io_threads()
+        # pwrite/pread workers per file; up to 16 files are in flight, and 16-32 threads in total already
+        # saturate tmpfs on the measured box (profiles/r01_box_peaks.json)
+        self._io_threads = knobs.get_io_threads() or 2
 
     def _prepare(self, rel: str) -> str:
         path = os.path.join(self.root, rel)
