@@ -10,9 +10,10 @@ from torchsnapshot_b200.snapshot import Snapshot, StateDict
 state=bench.build_state("cuda:0"); P=bench.payload_bytes(state)
 outs=StateDict({k: torch.empty_like(v) for k,v in state.items()})
 app={"ddp": StateDict(state)}
-for trial in range(4):
+NT=int(os.environ.get('TRIALS','4'))
+for trial in range(NT):
     d=tempfile.mkdtemp(dir="/dev/shm"); torch.cuda.synchronize()
-    prof = cProfile.Profile() if trial==3 else None
+    prof = cProfile.Profile() if (trial==3 and NT==4) else None
     t0=time.monotonic()
     if prof: prof.enable()
     snap=Snapshot.take(d, app, replicated=["**"])
@@ -23,7 +24,7 @@ for trial in range(4):
       "staging_done":rel(st.staging_done),"d2h_done":rel(st.d2h_done),"writes_done":rel(st.writes_done),"device_ms":round(st.device_ms(),1),"kernel_ms":round(st.kernel_ms(),2)}),flush=True)
     if prof:
         s=io.StringIO(); pstats.Stats(prof,stream=s).sort_stats("cumulative").print_stats(25); print(s.getvalue()[:3500])
-    prof = cProfile.Profile() if trial==3 else None
+    prof = cProfile.Profile() if (trial==3 and NT==4) else None
     t0=time.monotonic()
     if prof: prof.enable()
     snap.restore({"ddp": outs})

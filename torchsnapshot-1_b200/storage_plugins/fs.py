@@ -22,10 +22,12 @@ class FSStoragePlugin(StoragePlugin):
     def __init__(self, root: str, storage_options: Optional[Dict[str, Any]] = None) -> None:
         self.root = root
         self._dir_cache: Set[str] = set()
-        self._executor = ThreadPoolExecutor(max_workers=16, thread_name_prefix="tsb-fs")
-        # pwrite/pread workers per file; up to 16 files are in flight, and 16-32 threads in total already
+        self._executor = ThreadPoolExecutor(
+            max_workers=int(os.environ.get("TSB200_IO_CONCURRENCY", "32")), thread_name_prefix="tsb-fs"
+        )
+        # pwrite/pread workers per file; up to 32 files are in flight, and 16-32 threads in total already
         # saturate tmpfs on the measured box (profiles/r01_box_peaks.json)
-        self._io_threads = knobs.get_io_threads() or 2
+        self._io_threads = knobs.get_io_threads() or 1
 
     def _prepare(self, rel: str) -> str:
         path = os.path.join(self.root, rel)
