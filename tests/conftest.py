@@ -30,8 +30,10 @@ def _oracle_built():
     yield
 
 
-@pytest.fixture(scope="session")
+@pytest.fixture
 def engine():
+    # function scope on purpose: a test may shut the engines down (to change arena bounds), and
+    # get_engine() hands back the cached engine or builds a new one
     import torch
 
     if not torch.cuda.is_available():
