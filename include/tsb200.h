@@ -182,6 +182,38 @@ int tsb_copy_regions(TsbCtx* ctx, int stream, const TsbRegion* regions, uint32_t
 int tsb_copy_regions_timed(TsbCtx* ctx, int stream, const TsbRegion* regions, uint32_t n, TsbEvent* kernel_start,
                            TsbEvent* kernel_stop);
 
+/*
+ * The same multi-region copy for callers that must not allocate.  No counterpart in the reference.
+ *
+ * tsb_copy_regions takes its descriptor and tile tables from the context's arenas, which can end in
+ * cudaMalloc / cudaHostAlloc.  That is not acceptable everywhere: a trainer whose caching allocator
+ * already owns all of HBM (an extra cudaMalloc fails or eats into the pool), code that cannot afford
+ * the device-wide synchronisation cudaMalloc / cudaFree imply while other streams are busy, or an
+ * emergency path that wants to save state right after an out-of-memory error.  This entry point needs
+ * no context and allocates nothing, on the device or on the host: its scratch is one fixed array of
+ * TSB_STATIC_SCRATCH_BYTES inside the library, present on every GPU that loads the library for as long
+ * as the process lives.
+ *
+ *   device       CUDA device the addresses in `regions` belong to
+ *   cuda_stream  a cudaStream_t of that device (0 = legacy default stream); the copy is ordered on it
+ *   regions, n   as for tsb_copy_regions (host array, consumed before the call returns)
+ *
+ * Limits, checked before anything is launched (TSB_EINVAL and a message naming the limit): the
+ * descriptors of one call must fit TSB_STATIC_UPLOAD_BYTES (32 B per contiguous run, 32 B per 32 KiB of
+ * short-run strided payload plus 128 B per such region) and the contiguous payload must fit
+ * TSB_STATIC_MAX_TILES tiles of 32 KiB (1.5 GiB).  Split larger jobs into several calls on one stream.
+ *
+ * The first call on each device looks up the device address of the array (cudaGetSymbolAddress); make
+ * that first call before any stream capture begins.  All calls share the array and it keeps whatever
+ * the previous call left in it; nothing needs zeroing because each call rewrites every entry it reads,
+ * but two calls whose kernels can overlap on the GPU (different streams, no ordering between them)
+ * race on it -- keep such calls on one stream or order them with events.
+ */
+#define TSB_STATIC_SCRATCH_BYTES (2u * 1024u * 1024u)
+#define TSB_STATIC_UPLOAD_BYTES (512u * 1024u)
+#define TSB_STATIC_MAX_TILES ((TSB_STATIC_SCRATCH_BYTES - TSB_STATIC_UPLOAD_BYTES) / 32u)
+int tsb_copy_regions_static(int device, uint64_t cuda_stream, const TsbRegion* regions, uint32_t n);
+
 /* Device <-> pinned host copies on a context stream (K3 / K6). `hptr` should come from tsb_host_alloc. */
 int tsb_memcpy_d2h(TsbCtx* ctx, int stream, void* hptr, uint64_t dptr, uint64_t nbytes);
 int tsb_memcpy_h2d(TsbCtx* ctx, int stream, uint64_t dptr, const void* hptr, uint64_t nbytes);

@@ -73,6 +73,7 @@ _SIGNATURES = {
     "tsb_stream_sync": (_i, [_p, _i]),
     "tsb_copy_regions": (_i, [_p, _i, _p, ctypes.c_uint32]),
     "tsb_copy_regions_timed": (_i, [_p, _i, _p, ctypes.c_uint32, ctypes.POINTER(_u64), ctypes.POINTER(_u64)]),
+    "tsb_copy_regions_static": (_i, [_i, _u64, _p, ctypes.c_uint32]),
     "tsb_memcpy_d2h": (_i, [_p, _i, _p, _u64, _u64]),
     "tsb_memcpy_h2d": (_i, [_p, _i, _u64, _p, _u64]),
     "tsb_memcpy_d2d": (_i, [_p, _i, _u64, _u64, _u64]),
@@ -266,6 +267,15 @@ class Context:
 
     def peer_enable(self, peer_device: int) -> None:
         _check(self.lib, self.lib.tsb_peer_enable(self._h, peer_device))
+
+
+def copy_regions_static(device: int, cuda_stream: int, regions: np.ndarray) -> None:
+    """tsb_copy_regions_static: the multi-region copy for callers that may not allocate (no context,
+    scratch in a fixed array inside the library; limits in include/tsb200.h).  Ordered on `cuda_stream`."""
+    if regions.dtype != REGION_DTYPE or not regions.flags["C_CONTIGUOUS"]:
+        raise ValueError("regions must be a C-contiguous array of REGION_DTYPE")
+    lib = load_library()
+    _check(lib, lib.tsb_copy_regions_static(device, cuda_stream, regions.ctypes.data, int(regions.shape[0])))
 
 
 def host_memcpy(dst: int, src: int, nbytes: int, nthreads: int = 0) -> None:

@@ -749,6 +749,158 @@ int tsb_memcpy_d2d(TsbCtx* ctx, int stream, uint64_t dst, uint64_t src, uint64_t
   return TSB_OK;
 }
 
+// ---- copy without any allocation ----------------------------------------------------------------
+//
+// tsb_copy_regions needs scratch memory beyond its inputs and outputs: the descriptor tables it
+// uploads and the tile table the expansion kernel writes.  It takes that scratch from the context's
+// arenas, which may have to call cudaMalloc / cudaHostAlloc.  Some callers must not do that: a
+// process that has already handed every byte of HBM to its own memory pool (a cudaMalloc there fails
+// or steals from the pool), a hook that runs while another part of the program is in a phase where
+// the implicit device-wide synchronisation of cudaMalloc / cudaFree would stall its streams, or an
+// error / shutdown path that wants to push out a last copy after an out-of-memory condition.
+// For them the same kernels run out of the fixed array below.  The array exists once per GPU that
+// loads this library and stays for the life of the process, which is why it is small.
+//
+// Layout of the array:  [0, TSB_STATIC_UPLOAD_BYTES)   flat runs | strided tiles | strided regions
+//                       [TSB_STATIC_UPLOAD_BYTES, end)  flat tile table written by the expansion kernel
+// Nothing in it has to start at zero: every byte a kernel reads is written earlier in the same call
+// (upload, then expansion), so the leftovers of the previous call are never observed.
+static __device__ __align__(256) unsigned char g_static_scratch[TSB_STATIC_SCRATCH_BYTES];
+
+#define TSB_STATIC_MAX_DEVICES 64
+// `g_static_scratch` in host code is only a handle for the runtime; the address a kernel can use is
+// looked up once per device and kept here.
+static void* g_static_scratch_addr[TSB_STATIC_MAX_DEVICES];
+static bool g_static_scratch_ready[TSB_STATIC_MAX_DEVICES];
+static std::mutex g_static_mu;
+// host staging for the upload: fixed storage as well, protected by g_static_mu
+static unsigned char g_static_upload[TSB_STATIC_UPLOAD_BYTES] __attribute__((aligned(64)));
+
+extern "C" int tsb_copy_regions_static(int device, uint64_t cuda_stream, const TsbRegion* regions, uint32_t n) {
+  if (device < 0 || device >= TSB_STATIC_MAX_DEVICES) return set_err(TSB_EINVAL, "device %d out of range", device);
+  if (n == 0) return TSB_OK;
+  if (!regions) return set_err(TSB_EINVAL, "null regions");
+  DeviceGuard guard(device);
+  if (!guard.ok) return set_err(TSB_ECUDA, "cudaSetDevice(%d) failed", device);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_scratch_ready[device]) {
+    // set-up, once per device, with that device current
+    void* addr = nullptr;
+    cudaError_t se = cudaGetSymbolAddress(&addr, g_static_scratch);
+    if (se != cudaSuccess || addr == nullptr)
+      return set_err(TSB_ECUDA, "cudaGetSymbolAddress(static scratch) failed on device %d: %s", device,
+                     cudaGetErrorString(se));
+    g_static_scratch_addr[device] = addr;
+    g_static_scratch_ready[device] = true;
+  }
+  unsigned char* const dscratch = static_cast<unsigned char*>(g_static_scratch_addr[device]);
+
+  // pass 1: count, so that an oversized request is refused before anything is written
+  uint64_t n_runs = 0, n_flat_tiles = 0, n_str_tiles = 0, n_str_regions = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    const TsbRegion& r = regions[i];
+    int rc = validate_region(r, i);
+    if (rc != TSB_OK) return rc;
+    uint64_t total;
+    if (!region_payload(r, &total)) return set_err(TSB_EINVAL, "region %u: size overflow", i);
+    if (total == 0) continue;
+    if (r.ndim == 0) {
+      n_runs += 1;
+      n_flat_tiles += tsb_run_tiles(r.dst, r.run_bytes);
+    } else if (r.run_bytes >= TSB_FLAT_RUN_MIN) {
+      const uint64_t runs = total / r.run_bytes;
+      n_runs += runs;
+      // every run of the box: upper bound of its tiles (the exact count depends on each run's alignment)
+      n_flat_tiles += runs * (2 + r.run_bytes / TSB_TILE_BYTES);
+    } else {
+      uint64_t per = TSB_TILE_BYTES / r.run_bytes;
+      if (per == 0) per = 1;
+      const uint64_t step = per * r.run_bytes;
+      n_str_regions += 1;
+      n_str_tiles += (total + step - 1) / step;
+    }
+    if (n_runs > TSB_STATIC_UPLOAD_BYTES || n_flat_tiles > (1ull << 40)) break;  // far beyond any limit already
+  }
+  const uint64_t upload_need = n_runs * sizeof(TsbRun) + n_str_tiles * sizeof(TsbTile) + n_str_regions * sizeof(TsbRegion);
+  if (upload_need > TSB_STATIC_UPLOAD_BYTES)
+    return set_err(TSB_EINVAL,
+                   "tsb_copy_regions_static: descriptors need %llu bytes, the static scratch holds %llu "
+                   "(use tsb_copy_regions, or split the call)",
+                   (unsigned long long)upload_need, (unsigned long long)TSB_STATIC_UPLOAD_BYTES);
+  if (n_flat_tiles > TSB_STATIC_MAX_TILES)
+    return set_err(TSB_EINVAL,
+                   "tsb_copy_regions_static: %llu tiles of %u bytes needed, the static scratch holds %llu "
+                   "(about %llu MiB of payload per call; use tsb_copy_regions, or split the call)",
+                   (unsigned long long)n_flat_tiles, (unsigned)TSB_TILE_BYTES, (unsigned long long)TSB_STATIC_MAX_TILES,
+                   (unsigned long long)(TSB_STATIC_MAX_TILES * (uint64_t)TSB_TILE_BYTES >> 20));
+
+  // pass 2: fill the fixed host buffer: [runs][strided tiles][strided regions]
+  TsbRun* runs = reinterpret_cast<TsbRun*>(g_static_upload);
+  TsbTile* stiles = reinterpret_cast<TsbTile*>(g_static_upload + n_runs * sizeof(TsbRun));
+  TsbRegion* sregs = reinterpret_cast<TsbRegion*>(g_static_upload + n_runs * sizeof(TsbRun) + n_str_tiles * sizeof(TsbTile));
+  uint64_t ri = 0, ti = 0, gi = 0, tiles = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    const TsbRegion& r = regions[i];
+    uint64_t total = 0;
+    region_payload(r, &total);
+    if (total == 0) continue;
+    if (r.ndim == 0) {
+      runs[ri++] = TsbRun{r.src, r.dst, r.run_bytes, tiles};
+      tiles += tsb_run_tiles(r.dst, r.run_bytes);
+    } else if (r.run_bytes >= TSB_FLAT_RUN_MIN) {
+      uint64_t idx[TSB_MAX_DIMS] = {0, 0, 0, 0};
+      const uint64_t nr = total / r.run_bytes;
+      for (uint64_t q = 0; q < nr; ++q) {
+        int64_t so = 0, dofs = 0;
+        for (uint32_t d = 0; d < r.ndim; ++d) {
+          so += (int64_t)idx[d] * r.src_stride[d];
+          dofs += (int64_t)idx[d] * r.dst_stride[d];
+        }
+        runs[ri++] = TsbRun{r.src + so, r.dst + dofs, r.run_bytes, tiles};
+        tiles += tsb_run_tiles(r.dst + dofs, r.run_bytes);
+        for (int d = (int)r.ndim - 1; d >= 0; --d) {
+          if (++idx[d] < r.size[d]) break;
+          idx[d] = 0;
+        }
+      }
+    } else {
+      uint64_t per = TSB_TILE_BYTES / r.run_bytes;
+      if (per == 0) per = 1;
+      const uint64_t step = per * r.run_bytes;
+      for (uint64_t off = 0; off < total; off += step) {
+        TsbTile t;
+        t.src = 0;
+        t.dst = 0;
+        t.off = off;
+        t.len = (uint32_t)std::min<uint64_t>(step, total - off);
+        t.region = (uint32_t)gi;
+        stiles[ti++] = t;
+      }
+      sregs[gi++] = r;
+    }
+  }
+  if (ri == 0 && ti == 0) return TSB_OK;
+  cudaStream_t s = (cudaStream_t)(uintptr_t)cuda_stream;
+  // pageable source: the runtime has consumed g_static_upload when this returns, so the buffer can be
+  // reused by the next call as soon as the mutex is released
+  cudaError_t e = cudaMemcpyAsync(dscratch, g_static_upload, upload_need, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess && tiles) {
+    TsbTile* dtiles = reinterpret_cast<TsbTile*>(dscratch + TSB_STATIC_UPLOAD_BYTES);
+    tsb_expand_flat_kernel<<<((uint32_t)tiles + 255) / 256, 256, 0, s>>>(reinterpret_cast<const TsbRun*>(dscratch),
+                                                                        (uint32_t)ri, dtiles, (uint32_t)tiles);
+    tsb_copy_flat_kernel<<<(uint32_t)tiles, TSB_FLAT_THREADS, 0, s>>>(dtiles);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess && ti) {
+    tsb_copy_strided_kernel<<<(uint32_t)ti, TSB_STRIDED_THREADS, 0, s>>>(
+        reinterpret_cast<const TsbRegion*>(dscratch + ri * sizeof(TsbRun) + ti * sizeof(TsbTile)),
+        reinterpret_cast<const TsbTile*>(dscratch + ri * sizeof(TsbRun)));
+    e = cudaGetLastError();
+  }
+  if (e != cudaSuccess) return set_err(TSB_ECUDA, "tsb_copy_regions_static launch failed: %s", cudaGetErrorString(e));
+  return TSB_OK;
+}
+
 // ---- host helpers ---------------------------------------------------------------------------
 static int default_threads(uint64_t nbytes, int nthreads) {
   if (nthreads <= 0) {
