@@ -1,0 +1,129 @@
+"""Worker bodies for the world_size-2 gloo tests (spawned processes import this module by name)."""
+
+import os
+import sys
+import traceback
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch
+import torch.distributed as dist
+
+import tsb200_loader
+
+tsb200_loader.load()
+
+
+def _init(rank, world, port):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+
+
+def run(rank, world, port, fn_name, tmp, errq):
+    try:
+        _init(rank, world, port)
+        globals()[fn_name](rank, world, tmp)
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception:
+        errq.put(f"rank {rank}:\n{traceback.format_exc()}")
+        raise
+
+
+def _state(seed):
+    import _cases
+
+    return {
+        "w": _cases.raw_tensor(seed, [300, 40], torch.float32),
+        "b": _cases.raw_tensor(seed + 1, [77], torch.bfloat16 if False else torch.float16),
+        "big": _cases.raw_tensor(seed + 2, [64, 100], torch.float64),
+        "n": 7,
+    }
+
+
+def replicated_partition(rank, world, tmp):
+    """DDP-style replicated state: every replicated byte is written exactly once, by some rank."""
+    import json
+
+    from torchsnapshot_b200 import knobs
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    shared = StateDict(_state(100))
+    own = StateDict(r=torch.full((10,), float(rank)))
+    path = os.path.join(tmp, "snap")
+    with knobs.override_max_chunk_size_bytes(20000), knobs.override_slab_size_threshold_bytes(9000):
+        snap = Snapshot.take(path, {"shared": shared, "own": own}, replicated=["shared/**"])
+    dist.barrier()
+    meta = json.load(open(os.path.join(path, ".snapshot_metadata")))["manifest"]
+    assert meta["0/shared/w"]["type"] == "ChunkedTensor" and meta["0/shared/w"]["replicated"] is True
+    assert "1/shared/w" not in meta  # replicated entries are listed once, under rank 0
+    assert meta["0/own/r"]["replicated"] is False and "1/own/r" in meta
+    # every chunk of the replicated tensor exists exactly once on disk, written by either rank
+    chunks = meta["0/shared/w"]["chunks"]
+    assert [c["offsets"] for c in chunks] == sorted(c["offsets"] for c in chunks)
+    for c in chunks:
+        assert os.path.exists(os.path.join(path, c["tensor"]["location"]))
+    # both ranks restore the replicated state and their own state
+    out_shared = StateDict({k: (torch.zeros_like(v) if isinstance(v, torch.Tensor) else 0) for k, v in shared.items()})
+    out_own = StateDict(r=torch.zeros(10))
+    snap.restore({"shared": out_shared, "own": out_own})
+    for k, v in shared.items():
+        if isinstance(v, torch.Tensor):
+            assert torch.equal(out_shared[k], v), k
+    assert out_shared["n"] == 7 and torch.equal(out_own["r"], own["r"])
+    # the write load was split: both ranks wrote payload files of the replicated state
+    if rank == 0:
+        import glob
+
+        files = glob.glob(os.path.join(path, "replicated", "**", "*"), recursive=True) + glob.glob(
+            os.path.join(path, "batched", "*"))
+        assert len([f for f in files if os.path.isfile(f)]) >= 2
+
+
+def sharded_reshard(rank, world, tmp):
+    """ShardedTensor saved with rows split over the ranks, restored with columns split over them
+    (every rank needs bytes of every persisted piece), and read back as a dense tensor."""
+    import _cases
+    from torch.distributed._shard import sharded_tensor
+    from torch.distributed._shard.sharding_spec import ChunkShardingSpec
+
+    from torchsnapshot_b200 import knobs
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    full = _cases.raw_tensor(500, [48, 36], torch.float32)
+    src_spec = ChunkShardingSpec(dim=0, placements=[f"rank:{r}/cpu" for r in range(world)])
+    dst_spec = ChunkShardingSpec(dim=1, placements=[f"rank:{r}/cpu" for r in range(world)])
+    src = sharded_tensor.empty(src_spec, 48, 36)
+    for shard in src.local_shards():
+        shard.tensor.copy_(_cases.box_slice(full, (shard.metadata.shard_offsets, shard.metadata.shard_sizes)))
+    path = os.path.join(tmp, "snap")
+    with knobs.override_max_shard_size_bytes(5 * 36 * 4):
+        snap = Snapshot.take(path, {"emb": StateDict(t=src)})
+    m = snap.get_manifest()
+    pieces = [s for r in range(world) for s in m[f"{r}/emb/t"].shards]
+    assert len(pieces) == 10 and all(s.tensor.location.startswith("sharded/emb/t_") or s.tensor.location.startswith("batched/")
+                                     for s in pieces)
+    dst = sharded_tensor.empty(dst_spec, 48, 36)
+    snap.restore({"emb": StateDict(t=dst)})
+    for shard in dst.local_shards():
+        assert torch.equal(shard.tensor, _cases.box_slice(full, (shard.metadata.shard_offsets, shard.metadata.shard_sizes)))
+    dense = torch.zeros(48, 36)
+    got = snap.read_object("0/emb/t", obj_out=dense)
+    assert torch.equal(got, full)
+
+
+def async_commit(rank, world, tmp):
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    state = StateDict(t=torch.arange(1000, dtype=torch.float32) + rank)
+    pending = Snapshot.async_take(os.path.join(tmp, "snap"), {"s": state})
+    state["t"].zero_()
+    snap = pending.wait()
+    out = StateDict(t=torch.zeros(1000))
+    snap.restore({"s": out})
+    assert torch.equal(out["t"], torch.arange(1000, dtype=torch.float32) + rank)
+    assert os.path.exists(os.path.join(tmp, "snap", ".snapshot_metadata"))

@@ -1,0 +1,50 @@
+"""The N > 1 path on CPU: world_size-2 gloo process groups (replicated-write partitioning, manifest
+gather, sharded take + reshard-restore, async commit through the store)."""
+
+import socket
+
+import pytest
+import torch.multiprocessing as mp
+
+import _dist_workers
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _launch(fn_name, tmp_path, world=2):
+    ctx = mp.get_context("spawn")
+    errq = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_dist_workers.run, args=(r, world, port, fn_name, str(tmp_path), errq)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=180)
+    errs = []
+    while not errq.empty():
+        errs.append(errq.get())
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+            errs.append("worker timed out")
+    assert not errs, "\n".join(errs)
+    assert all(p.exitcode == 0 for p in procs)
+
+
+@pytest.mark.timeout(300)
+def test_replicated_writes_are_partitioned(tmp_path):
+    _launch("replicated_partition", tmp_path)
+
+
+@pytest.mark.timeout(300)
+def test_sharded_take_and_reshard_restore(tmp_path):
+    _launch("sharded_reshard", tmp_path)
+
+
+@pytest.mark.timeout(300)
+def test_async_take_commit_across_ranks(tmp_path):
+    _launch("async_commit", tmp_path)
