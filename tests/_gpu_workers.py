@@ -1,0 +1,107 @@
+"""Worker bodies for the multi-GPU tests (one process per GPU, NCCL process group)."""
+
+import os
+import sys
+import traceback
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch
+import torch.distributed as dist
+
+import tsb200_loader
+
+tsb200_loader.load()
+
+
+def run(rank, world, port, fn_name, tmp, errq):
+    try:
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+        globals()[fn_name](rank, world, tmp)
+        dist.barrier(device_ids=[rank])
+        dist.destroy_process_group()
+    except Exception:
+        errq.put(f"rank {rank}:\n{traceback.format_exc()}")
+        raise
+
+
+def _sharded(spec_dim, world, shape, full=None):
+    import _cases
+    from torch.distributed._shard import sharded_tensor
+    from torch.distributed._shard.sharding_spec import ChunkShardingSpec
+
+    spec = ChunkShardingSpec(dim=spec_dim, placements=[f"rank:{r}/cuda:{r}" for r in range(world)])
+    st = sharded_tensor.empty(spec, *shape, dtype=torch.float32)
+    for shard in st.local_shards():
+        if full is not None:
+            shard.tensor.copy_(_cases.box_slice(full, (shard.metadata.shard_offsets, shard.metadata.shard_sizes)))
+        else:
+            shard.tensor.zero_()
+    return st
+
+
+def p2p_reshard(rank, world, tmp):
+    """Rows saved, columns restored: every rank needs a slice of every persisted piece.  The P2P path
+    (each piece read once, the rest over NVLink) must give the bytes of the storage-only path."""
+    import _cases
+    from torchsnapshot_b200 import knobs, reshard
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    shape = [1024, 640]
+    full = _cases.raw_tensor(77, shape, torch.float32)
+    src = _sharded(0, world, shape, full)
+    own = StateDict(x=torch.full((5,), float(rank), device="cuda"))
+    path = os.path.join(tmp, "snap")
+    with knobs.override_max_shard_size_bytes(100 * 640 * 4):
+        snap = Snapshot.take(path, {"emb": StateDict(t=src), "own": own})
+    # P2P restore into a column-wise layout
+    dst = _sharded(1, world, shape)
+    out_own = StateDict(x=torch.zeros(5, device="cuda"))
+    snap.restore({"emb": StateDict(t=dst), "own": out_own})
+    st = reshard.last_stats
+    assert st is not None and st.launches == 1 and st.peer_bytes > 0, vars(st) if st else None
+    total = 1024 * 640 * 4
+    assert st.local_bytes + st.peer_bytes == total // world
+    for shard in dst.local_shards():
+        want = _cases.box_slice(full, (shard.metadata.shard_offsets, shard.metadata.shard_sizes)).cuda()
+        assert torch.equal(shard.tensor, want)
+    assert torch.equal(out_own["x"], own["x"])
+    # the storage-only path (reference semantics) gives the same bytes
+    os.environ["TSB200_P2P_RESHARD"] = "0"
+    try:
+        dst2 = _sharded(1, world, shape)
+        reshard.last_stats = None
+        snap.restore({"emb": StateDict(t=dst2), "own": out_own})
+        assert reshard.last_stats is None
+        for a, b in zip(dst.local_shards(), dst2.local_shards()):
+            assert torch.equal(a.tensor, b.tensor)
+    finally:
+        del os.environ["TSB200_P2P_RESHARD"]
+    # row-wise -> row-wise at the same world size: no peer traffic at all
+    dst3 = _sharded(0, world, shape)
+    snap.restore({"emb": StateDict(t=dst3), "own": out_own})
+    assert reshard.last_stats.peer_bytes == 0 and reshard.last_stats.local_bytes == total // world
+    for a, b in zip(src.local_shards(), dst3.local_shards()):
+        assert torch.equal(a.tensor, b.tensor)
+
+
+def ddp_replicated(rank, world, tmp):
+    """Replicated CUDA state partitioned over the ranks; every rank restores all of it."""
+    import _cases
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    state = StateDict({f"p{i}": _cases.raw_tensor(200 + i, [257, 33 + i], torch.float32).cuda() for i in range(12)})
+    state["step"] = torch.tensor(3.0, device="cuda")
+    snap = Snapshot.take(os.path.join(tmp, "snap"), {"m": state}, replicated=["**"])
+    out = StateDict({k: torch.zeros_like(v) for k, v in state.items()})
+    snap.restore({"m": out})
+    for k in state:
+        assert torch.equal(out[k], state[k]), k
+    m = snap.get_manifest()
+    assert all(m[f"0/m/p{i}"].replicated for i in range(12)) and "1/m/p0" not in m

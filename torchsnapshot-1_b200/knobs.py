@@ -47,6 +47,12 @@ def get_pinned_bytes(default: int) -> int:
     return _int_env(_PINNED_ENV_VAR, default)
 
 
+def is_p2p_reshard_enabled() -> bool:
+    """Peer-to-peer reshard-restore of sharded CUDA tensors (reshard.py); TSB200_P2P_RESHARD=0 forces the
+    reference's storage-only path."""
+    return os.getenv("TSB200_P2P_RESHARD", "1").lower() not in ("0", "false")
+
+
 def get_io_threads() -> int:
     return _int_env(_IO_THREADS_ENV_VAR, 0)
 

@@ -314,9 +314,13 @@ class Snapshot:
         local_world = sum(1 for k in keys if k[1] == keys[rank][1])
         budget = _memory_budget(local_world)
         rng_key = rng_items[0][0] if rng_items else None
+        # keys every rank restores: only those can use the collective peer-to-peer reshard path
+        on_all_ranks = set.intersection(*(set(k[0]) for k in keys))
         for key in global_keys:
             if key != rng_key:
-                self._load_stateful(key, app_state.get(key), storage, rank, budget, event_loop)
+                p2p_pg = pg if (world > 1 and key in on_all_ranks and knobs.is_p2p_reshard_enabled()
+                                and torch.cuda.is_available()) else None
+                self._load_stateful(key, app_state.get(key), storage, rank, budget, event_loop, p2p_pg)
             if world > 1:
                 pg.barrier()
         if rng_key is not None:  # RNG state last, so loading has no side effect on it
@@ -326,7 +330,7 @@ class Snapshot:
 
     def _load_stateful(
         self, key: str, stateful: Optional[Any], storage: StoragePlugin, rank: int, budget: int,
-        event_loop: asyncio.AbstractEventLoop,
+        event_loop: asyncio.AbstractEventLoop, p2p_pg: Optional[PGWrapper] = None,
     ) -> None:
         if stateful is None:
             return
@@ -342,11 +346,32 @@ class Snapshot:
         containers: Manifest = {}
         read_reqs: List[ReadReq] = []
         futs: Dict[str, Any] = {}
+        # sharded tensors on CUDA, restored by every rank: each persisted piece is read from storage by ONE
+        # rank and reaches the others over NVLink (reshard.py); the rest takes the ordinary path below
+        p2p_done: Dict[str, Any] = {}
+        if p2p_pg is not None:
+            from . import reshard
+
+            device = torch.cuda.current_device() if torch.cuda.is_available() else -1
+            cand = [
+                (lp, e, flattened[lp])
+                for lp, e in manifest.items()
+                if isinstance(e, ShardedTensorEntry) and lp in flattened and lp.split("/")[0] == prefix
+                and device >= 0 and reshard.eligible(e, flattened[lp], device)
+            ]
+            rstats = reshard.p2p_reshard_restore(cand, storage, p2p_pg, event_loop, max(device, 0))
+            p2p_done = {lp: obj for lp, _e, obj in cand if lp not in rstats.skipped}
         for logical_path, entry in manifest.items():
             if logical_path.split("/")[0] != prefix:
                 continue
             if is_container_entry(entry):
                 containers[logical_path] = entry
+                continue
+            if logical_path in p2p_done:
+                from .io_types import Future
+
+                futs[logical_path] = Future(obj=p2p_done[logical_path])
+                flattened.pop(logical_path, None)
                 continue
             if isinstance(entry, ShardedTensorEntry) and logical_path not in flattened:
                 continue  # sharded entries can only be loaded into a runtime object
