@@ -258,6 +258,11 @@ __device__ __forceinline__ void copy_span(uint8_t* __restrict__ dst, const uint8
 // Byte offsets of run q of a strided region on the source and destination side.
 __device__ __forceinline__ void run_offsets(const TsbRegion* __restrict__ r, uint32_t ndim, uint64_t q, int64_t& so,
                                             int64_t& dofs) {
+  if (ndim == 1) {  // pitched rows, the common case: no division at all
+    so = (int64_t)q * __ldg(&r->src_stride[0]);
+    dofs = (int64_t)q * __ldg(&r->dst_stride[0]);
+    return;
+  }
   so = 0;
   dofs = 0;
   for (int d = (int)ndim - 1; d >= 0; --d) {
@@ -275,25 +280,41 @@ __device__ __forceinline__ void run_offsets(const TsbRegion* __restrict__ r, uin
   }
 }
 
+// Unit-wise copy: unit u of the tile is element k of run q; consecutive threads take consecutive units,
+// so accesses stay coalesced within a run and across adjacent runs.  Four units per thread are loaded
+// before the first is stored.
 template <typename T>
 __device__ __forceinline__ void copy_units(const TsbRegion* __restrict__ r, uint64_t src, uint64_t dst, uint32_t ndim,
                                            uint64_t first_unit, uint64_t nunits, uint32_t units_per_run,
                                            uint32_t tid) {
-  for (uint64_t u = tid; u < nunits; u += TSB_STRIDED_THREADS) {
-    const uint64_t f = first_unit + u;
-    uint64_t q, k;
-    if ((f >> 32) == 0) {
-      q = (uint32_t)f / units_per_run;
-      k = (uint32_t)f % units_per_run;
-    } else {
-      q = f / units_per_run;
-      k = f % units_per_run;
+  constexpr int U = 4;
+  for (uint64_t base = 0; base < nunits; base += (uint64_t)U * TSB_STRIDED_THREADS) {
+    T v[U];
+    T* dp[U];
+    bool ok[U];
+#pragma unroll
+    for (int i = 0; i < U; ++i) {
+      const uint64_t u = base + tid + (uint64_t)i * TSB_STRIDED_THREADS;
+      ok[i] = u < nunits;
+      if (ok[i]) {
+        const uint64_t f = first_unit + u;
+        uint64_t q, k;
+        if ((f >> 32) == 0) {
+          q = (uint32_t)f / units_per_run;
+          k = (uint32_t)f % units_per_run;
+        } else {
+          q = f / units_per_run;
+          k = f % units_per_run;
+        }
+        int64_t so, dofs;
+        run_offsets(r, ndim, q, so, dofs);
+        v[i] = *(reinterpret_cast<const T*>(src + so) + k);
+        dp[i] = reinterpret_cast<T*>(dst + dofs) + k;
+      }
     }
-    int64_t so, dofs;
-    run_offsets(r, ndim, q, so, dofs);
-    const T* sp = reinterpret_cast<const T*>(src + so) + k;
-    T* dp = reinterpret_cast<T*>(dst + dofs) + k;
-    *dp = *sp;
+#pragma unroll
+    for (int i = 0; i < U; ++i)
+      if (ok[i]) *dp[i] = v[i];
   }
 }
 
@@ -314,7 +335,13 @@ tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __
   const uint32_t ndim = rb.z;
 
   // runs of TSB_FLAT_RUN_MIN bytes or more never get here: the host expands them into flat tiles
-  if (run_bytes >= TSB_WARP_RUN_MIN) {
+  // the widest power-of-two unit (1..16 bytes) every address of the region is aligned to
+  uint64_t m = src | dst | run_bytes | 16u;
+  for (uint32_t d = 0; d < ndim; ++d) m |= (uint64_t)__ldg(&r->src_stride[d]) | (uint64_t)__ldg(&r->dst_stride[d]);
+  const uint32_t unit = (uint32_t)(m & (~m + 1));
+  // Runs of 64 bytes or more whose addresses are NOT all 16-byte aligned go one per warp (the span copy
+  // realigns them); aligned runs and runs under 64 bytes are copied unit by unit.
+  if (run_bytes >= TSB_WARP_RUN_MIN && unit < 16u) {
     // the host emits whole runs per tile for this class
     const uint64_t q0 = off / run_bytes;
     const uint32_t nruns = len / (uint32_t)run_bytes;
@@ -327,10 +354,6 @@ tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __
     }
     return;
   }
-  // element mode: the widest power-of-two unit every address of the region is aligned to
-  uint64_t m = src | dst | run_bytes | 16u;
-  for (uint32_t d = 0; d < ndim; ++d) m |= (uint64_t)__ldg(&r->src_stride[d]) | (uint64_t)__ldg(&r->dst_stride[d]);
-  const uint32_t unit = (uint32_t)(m & (~m + 1));  // lowest set bit: 1, 2, 4, 8 or 16
   const uint32_t upr = (uint32_t)run_bytes / unit;
   const uint64_t first = off / unit;
   const uint64_t nunits = len / unit;

@@ -157,7 +157,6 @@ def p2p_reshard_restore(
     from .scheduler import _Allocator, _read_into_pinned  # shared read machinery
 
     stats = ReshardStats()
-    last_stats = stats
     rank, world = pg.get_rank(), pg.get_world_size()
 
     # ---- 1. everybody's local boxes (metadata all-gather), then the plan ------------------------------
@@ -177,6 +176,7 @@ def p2p_reshard_restore(
         pieces += pieces_of(path, entry)
     if not pieces:
         return stats
+    last_stats = stats  # only calls that had something to do are remembered
     eng = get_engine(device)
     ctx = eng.ctx
     owners = plan_owners(pieces, gathered)
