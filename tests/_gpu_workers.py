@@ -100,8 +100,27 @@ def ddp_replicated(rank, world, tmp):
     state["step"] = torch.tensor(3.0, device="cuda")
     snap = Snapshot.take(os.path.join(tmp, "snap"), {"m": state}, replicated=["**"])
     out = StateDict({k: torch.zeros_like(v) for k, v in state.items()})
+    from torchsnapshot_b200 import reshard
+
+    reshard.last_stats = None
     snap.restore({"m": out})
     for k in state:
         assert torch.equal(out[k], state[k]), k
+    # replicated restore: every byte is read from storage by one rank only; the other gets it over NVLink
+    st = reshard.last_stats
+    total = sum(v.numel() * v.element_size() for v in state.values())
+    t = torch.tensor([st.read_bytes, st.peer_bytes, st.local_bytes], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t)
+    assert int(t[0].item()) == total, (t.tolist(), total)
+    assert int(t[1].item()) + int(t[2].item()) == total * world and st.peer_bytes > 0
+    # and the storage-only path agrees
+    os.environ["TSB200_P2P_RESHARD"] = "0"
+    try:
+        out2 = StateDict({k: torch.zeros_like(v) for k, v in state.items()})
+        snap.restore({"m": out2})
+        for k in state:
+            assert torch.equal(out2[k], state[k]), k
+    finally:
+        del os.environ["TSB200_P2P_RESHARD"]
     m = snap.get_manifest()
     assert all(m[f"0/m/p{i}"].replicated for i in range(12)) and "1/m/p0" not in m

@@ -22,7 +22,7 @@ import asyncio
 import logging
 from concurrent.futures import ThreadPoolExecutor
 from dataclasses import dataclass
-from typing import Any, Dict, List, Optional, Sequence, Tuple
+from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
 
 import torch
 
@@ -132,58 +132,133 @@ def eligible(entry: ShardedTensorEntry, obj_out: Any, device: int) -> bool:
 
 class ReshardStats:
     def __init__(self) -> None:
-        self.read_bytes = 0  # bytes this rank read from storage (it owns these pieces)
+        self.read_bytes = 0  # bytes this rank read from storage (it owns these units)
         self.local_bytes = 0  # bytes copied from this rank's own staging
         self.peer_bytes = 0  # bytes this rank pulled over NVLink
         self.copy_ms = 0.0  # device time of the copy kernels (CUDA events)
         self.launches = 0
-        self.skipped: List[str] = []  # paths some rank did not offer: load them through the ordinary path
+        self.skipped: List[str] = []  # sharded paths some rank did not offer: load them the ordinary way
 
 
 last_stats: Optional[ReshardStats] = None
 
+UnitKey = Tuple[str, int, int]  # (storage location, lower byte, upper byte; -1,-1 = whole object)
 
-def p2p_reshard_restore(
-    items: Sequence[Tuple[str, ShardedTensorEntry, Any]],
+
+@dataclass
+class Unit:
+    """A byte range of one storage object that one or more ranks need on the device: a persisted piece
+    of a sharded tensor, or the merged range of the replicated members of a slab file."""
+
+    location: str
+    byte_range: Optional[Tuple[int, int]]
+    nbytes: int
+    need: int  # payload bytes THIS rank takes out of the unit
+    regions: Callable[[int], List[RegionTuple]]  # device address of the unit's first byte -> copy regions
+
+    @property
+    def key(self) -> UnitKey:
+        br = self.byte_range
+        return (self.location, br[0], br[1]) if br is not None else (self.location, -1, -1)
+
+
+def plan_unit_owners(needs_by_rank: Sequence[Dict[UnitKey, Tuple[int, int]]]) -> Dict[UnitKey, int]:
+    """Owner rank per unit from every rank's {key: (need bytes, unit bytes)}; same rule as plan_owners."""
+    load = [0] * len(needs_by_rank)
+    owners: Dict[UnitKey, int] = {}
+    for key in sorted(set().union(*(d.keys() for d in needs_by_rank))):
+        need = [d.get(key, (0, 0))[0] for d in needs_by_rank]
+        nbytes = max(d.get(key, (0, 0))[1] for d in needs_by_rank)
+        best = max(need)
+        if best == 0:
+            continue
+        candidates = [r for r, n in enumerate(need) if n * 1000 >= best * 999]
+        owner = min(candidates, key=lambda r: (load[r], r))
+        load[owner] += nbytes
+        owners[key] = owner
+    return owners
+
+
+def sharded_units(items: Sequence[Tuple[str, ShardedTensorEntry, Any]]) -> List[Unit]:
+    """Units (one per persisted piece this rank overlaps) for sharded tensors restored into CUDA shards."""
+    units: List[Unit] = []
+    for path, entry, obj in items:
+        locals_ = ShardedTensorIOPreparer.local_boxes(obj)
+        for piece in pieces_of(path, entry):
+            elsize = dtype_to_element_size(string_to_dtype(piece.dtype))
+            overlaps = []
+            need = 0
+            for tensor, off, sizes in locals_:
+                region = overlap_wrt_saved(piece.offsets, piece.sizes, off, sizes)
+                if region is None:
+                    continue
+                n = elsize
+                for _d, _so, _do, length in region:
+                    n *= length
+                need += n
+                overlaps.append((tensor, region))
+            if not overlaps:
+                continue
+
+            def make(base: int, piece: Piece = piece, overlaps: Any = overlaps, elsize: int = elsize) -> List[RegionTuple]:
+                src_strides = contiguous_strides(piece.sizes, elsize)
+                out: List[RegionTuple] = []
+                for tensor, region in overlaps:
+                    dst = tensor.detach()
+                    dst_strides = [s * elsize for s in dst.stride()]
+                    src_addr, dst_addr, lens = base, dst.data_ptr(), []
+                    for dim, so, do, length in region:
+                        src_addr += so * src_strides[dim]
+                        dst_addr += do * dst_strides[dim]
+                        lens.append(length)
+                    out += box_regions(src_addr, src_strides, dst_addr, dst_strides, lens, elsize)
+                return out
+
+            units.append(Unit(piece.location, piece.byte_range, piece.nbytes, need, make))
+    return units
+
+
+def read_req_units(read_reqs: Sequence[ReadReq]) -> List[Unit]:
+    """Units for (batched) read requests whose consumers can unpack on the device (replicated state)."""
+    units = []
+    for rr in read_reqs:
+        c = rr.buffer_consumer
+        n = rr.byte_range[1] - rr.byte_range[0] if rr.byte_range is not None else c.consumed_nbytes()
+        units.append(Unit(rr.path, rr.byte_range, n, n, c.unpack_regions))
+    return units
+
+
+def p2p_restore_units(
+    units: Sequence[Unit],
     storage: StoragePlugin,
     pg: Any,
     event_loop: asyncio.AbstractEventLoop,
     device: int,
 ) -> ReshardStats:
-    """Restore `items` = (logical path, merged sharded entry, runtime object) on every rank of `pg`.
-    Collective: every rank of `pg` must call it (possibly with an empty list).  Only the paths that every
-    rank passed are handled; `stats.skipped` lists the others so the caller can load them the ordinary way."""
+    """Collective over `pg` (every rank calls it, possibly with no units): each unit is read from storage
+    by ONE rank, and every rank that needs it copies out of that rank's device staging -- its own, or a
+    peer's through a CUDA IPC mapping, i.e. over NVLink."""
     global last_stats
     from .scheduler import _Allocator, _read_into_pinned  # shared read machinery
 
     stats = ReshardStats()
     rank, world = pg.get_rank(), pg.get_world_size()
-
-    # ---- 1. everybody's local boxes (metadata all-gather), then the plan ------------------------------
-    my_boxes: Dict[str, List[Box]] = {}
-    my_tensors: Dict[str, List[torch.Tensor]] = {}
-    for path, _entry, obj in items:
-        locals_ = ShardedTensorIOPreparer.local_boxes(obj)
-        my_boxes[path] = [(list(o), list(s)) for _t, o, s in locals_]
-        my_tensors[path] = [t for t, _o, _s in locals_]
+    mine_by_key = {u.key: u for u in units}
     gathered: List[Any] = [None] * world
-    pg.all_gather_object(gathered, my_boxes)
-    common = set.intersection(*(set(g.keys()) for g in gathered))
-    stats.skipped = [path for path, _e, _o in items if path not in common]
-    items = [it for it in items if it[0] in common]
-    pieces: List[Piece] = []
-    for path, entry, _obj in items:
-        pieces += pieces_of(path, entry)
-    if not pieces:
+    pg.all_gather_object(gathered, {k: (u.need, u.nbytes) for k, u in mine_by_key.items()})
+    owners = plan_unit_owners(gathered)
+    if not owners:
         return stats
     last_stats = stats  # only calls that had something to do are remembered
     eng = get_engine(device)
     ctx = eng.ctx
-    owners = plan_owners(pieces, gathered)
-
-    # ---- 2. owners read their pieces into device staging ------------------------------------------------
-    mine = [i for i, o in enumerate(owners) if o == rank]
-    staged: Dict[int, int] = {}  # piece index -> device address
+    sizes = {}
+    locations = {}
+    for d in gathered:
+        for k, (_need, nbytes) in d.items():
+            sizes[k] = max(sizes.get(k, 0), nbytes)
+    owned = [k for k, o in owners.items() if o == rank]
+    staged: Dict[UnitKey, int] = {}
 
     async def read_all() -> None:
         loop = asyncio.get_running_loop()
@@ -191,16 +266,17 @@ def p2p_reshard_restore(
         alloc = _Allocator()
         sem = asyncio.Semaphore(32)
 
-        async def one(i: int) -> None:
-            piece = pieces[i]
+        async def one(key: UnitKey) -> None:
+            nbytes = sizes[key]
+            br = None if key[1] < 0 else (key[1], key[2])
             async with sem:
-                dptr = await alloc.device(eng, piece.nbytes)
-                staged[i] = dptr
-                pbuf = await alloc.pinned(eng, piece.nbytes)
+                dptr = await alloc.device(eng, nbytes)
+                staged[key] = dptr
+                pbuf = await alloc.pinned(eng, nbytes)
                 try:
-                    rr = ReadReq(path=piece.location, buffer_consumer=None, byte_range=piece.byte_range)  # type: ignore
-                    await _read_into_pinned(loop, executor, storage, rr, pbuf, piece.nbytes)
-                    ctx.memcpy_h2d(STREAM_H2D, dptr, pbuf.ptr, piece.nbytes)
+                    rr = ReadReq(path=key[0], buffer_consumer=None, byte_range=br)  # type: ignore[arg-type]
+                    await _read_into_pinned(loop, executor, storage, rr, pbuf, nbytes)
+                    ctx.memcpy_h2d(STREAM_H2D, dptr, pbuf.ptr, nbytes)
                     ev = ctx.event_record(STREAM_H2D)
                     try:
                         await loop.run_in_executor(executor, ctx.event_sync, ev)
@@ -209,59 +285,38 @@ def p2p_reshard_restore(
                 finally:
                     pbuf.release()
                     alloc.notify()
-            stats.read_bytes += piece.nbytes
+            stats.read_bytes += nbytes
 
         try:
-            await asyncio.gather(*(one(i) for i in mine))
+            await asyncio.gather(*(one(k) for k in owned))
         finally:
             executor.shutdown(wait=False)
 
     try:
         event_loop.run_until_complete(read_all())
-
-        # ---- 3. publish where every piece lives (IPC handle of its arena segment + offset) --------------
-        exports = {i: ctx.ipc_export(dptr) for i, dptr in staged.items()}
+        # publish where every unit lives (IPC handle of its arena segment + offset); the all-gather also
+        # tells everybody that all units are resident
+        exports = {k: ctx.ipc_export(dptr) for k, dptr in staged.items()}
         all_exports: List[Any] = [None] * world
-        pg.all_gather_object(all_exports, exports)  # doubles as "all pieces are resident"
-
-        # ---- 4. one launch: own staging + peer staging -> local shards -----------------------------------
+        pg.all_gather_object(all_exports, exports)
         opened: Dict[Tuple[int, bytes], int] = {}
         regions: List[RegionTuple] = []
         try:
-            for i, piece in enumerate(pieces):
-                owner = owners[i]
-                if owner is None:
+            for key, unit in mine_by_key.items():
+                owner = owners.get(key)
+                if owner is None or unit.need == 0:
                     continue
-                elsize = dtype_to_element_size(string_to_dtype(piece.dtype))
-                src_strides = contiguous_strides(piece.sizes, elsize)
-                base: Optional[int] = None
-                for tensor, box in zip(my_tensors[piece.path], my_boxes[piece.path]):
-                    region = overlap_wrt_saved(piece.offsets, piece.sizes, box[0], box[1])
-                    if region is None:
-                        continue
-                    if base is None:
-                        if owner == rank:
-                            base = staged[i]
-                        else:
-                            handle, offset = all_exports[owner][i]
-                            key = (owner, handle)
-                            if key not in opened:
-                                opened[key] = ctx.ipc_open(handle)
-                            base = opened[key] + offset
-                    dst = tensor.detach()
-                    dst_strides = [s * elsize for s in dst.stride()]
-                    src_addr, dst_addr, lens = base, dst.data_ptr(), []
-                    nbytes = elsize
-                    for dim, so, do, length in region:
-                        src_addr += so * src_strides[dim]
-                        dst_addr += do * dst_strides[dim]
-                        lens.append(length)
-                        nbytes *= length
-                    regions += box_regions(src_addr, src_strides, dst_addr, dst_strides, lens, elsize)
-                    if owner == rank:
-                        stats.local_bytes += nbytes
-                    else:
-                        stats.peer_bytes += nbytes
+                if owner == rank:
+                    base = staged[key]
+                    stats.local_bytes += unit.need
+                else:
+                    handle, offset = all_exports[owner][key]
+                    hk = (owner, handle)
+                    if hk not in opened:
+                        opened[hk] = ctx.ipc_open(handle)
+                    base = opened[hk] + offset
+                    stats.peer_bytes += unit.need
+                regions += unit.regions(base)
             arr = regions_to_array(regions)
             if arr.shape[0]:
                 eng.wait_current_stream(STREAM_PACK)
@@ -271,8 +326,7 @@ def p2p_reshard_restore(
                 stats.launches += 1
                 ctx.event_release(k0)
                 ctx.event_release(k1)
-            # ---- 5. nobody may free its staging while a peer still reads it ------------------------------
-            pg.barrier()
+            pg.barrier()  # nobody may free its staging while a peer still reads it
         finally:
             for base_addr in opened.values():
                 ctx.ipc_close(base_addr)
@@ -280,3 +334,16 @@ def p2p_reshard_restore(
         for dptr in staged.values():
             ctx.dev_free(dptr)
     return stats
+
+
+def p2p_reshard_restore(
+    items: Sequence[Tuple[str, ShardedTensorEntry, Any]],
+    storage: StoragePlugin,
+    pg: Any,
+    event_loop: asyncio.AbstractEventLoop,
+    device: int,
+    extra_units: Sequence[Unit] = (),
+) -> ReshardStats:
+    """Restore sharded `items` = (logical path, merged entry, runtime object), plus any `extra_units`
+    (replicated state), with one shared-read + peer-copy round.  Collective over `pg`."""
+    return p2p_restore_units(list(sharded_units(items)) + list(extra_units), storage, pg, event_loop, device)

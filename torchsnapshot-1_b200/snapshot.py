@@ -346,39 +346,52 @@ class Snapshot:
         containers: Manifest = {}
         read_reqs: List[ReadReq] = []
         futs: Dict[str, Any] = {}
-        # sharded tensors on CUDA, restored by every rank: each persisted piece is read from storage by ONE
-        # rank and reaches the others over NVLink (reshard.py); the rest takes the ordinary path below
-        p2p_done: Dict[str, Any] = {}
-        if p2p_pg is not None:
-            from . import reshard
-
-            device = torch.cuda.current_device() if torch.cuda.is_available() else -1
-            cand = [
-                (lp, e, flattened[lp])
-                for lp, e in manifest.items()
-                if isinstance(e, ShardedTensorEntry) and lp in flattened and lp.split("/")[0] == prefix
-                and device >= 0 and reshard.eligible(e, flattened[lp], device)
-            ]
-            rstats = reshard.p2p_reshard_restore(cand, storage, p2p_pg, event_loop, max(device, 0))
-            p2p_done = {lp: obj for lp, _e, obj in cand if lp not in rstats.skipped}
+        # Sharded tensors and replicated state restored into CUDA tensors by every rank: each persisted
+        # piece / slab range is read from storage by ONE rank and reaches the others over NVLink
+        # (reshard.py); everything else takes the ordinary path below.
+        device = torch.cuda.current_device() if (p2p_pg is not None and torch.cuda.is_available()) else -1
+        sharded_p2p: List[Tuple[str, ShardedTensorEntry, Any]] = []
+        shared_read_reqs: List[ReadReq] = []
         for logical_path, entry in manifest.items():
             if logical_path.split("/")[0] != prefix:
                 continue
             if is_container_entry(entry):
                 containers[logical_path] = entry
                 continue
-            if logical_path in p2p_done:
-                from .io_types import Future
+            obj_out = flattened.get(logical_path)
+            if isinstance(entry, ShardedTensorEntry):
+                if obj_out is None:
+                    continue  # sharded entries can only be loaded into a runtime object
+                if device >= 0:
+                    from . import reshard
 
-                futs[logical_path] = Future(obj=p2p_done[logical_path])
-                flattened.pop(logical_path, None)
-                continue
-            if isinstance(entry, ShardedTensorEntry) and logical_path not in flattened:
-                continue  # sharded entries can only be loaded into a runtime object
-            rrs, fut = prepare_read(entry=entry, obj_out=flattened.get(logical_path))
-            read_reqs += rrs
+                    if reshard.eligible(entry, obj_out, device):
+                        sharded_p2p.append((logical_path, entry, obj_out))
+                        from .io_types import Future
+
+                        futs[logical_path] = Future(obj=obj_out)
+                        flattened.pop(logical_path, None)
+                        continue
+            rrs, fut = prepare_read(entry=entry, obj_out=obj_out)
+            if (
+                device >= 0
+                and is_replicated(entry)
+                and rrs
+                and all(getattr(rr.buffer_consumer, "is_device_consumable", lambda: False)() for rr in rrs)
+            ):
+                shared_read_reqs += rrs
+            else:
+                read_reqs += rrs
             futs[logical_path] = fut
             flattened.pop(logical_path, None)
+        if p2p_pg is not None and device >= 0:
+            from . import reshard
+
+            if not knobs.is_batching_disabled():
+                shared_read_reqs = batch_read_requests(read_reqs=shared_read_reqs)
+            reshard.p2p_reshard_restore(
+                sharded_p2p, storage, p2p_pg, event_loop, device, extra_units=reshard.read_req_units(shared_read_reqs)
+            )
         if not knobs.is_batching_disabled():
             read_reqs = batch_read_requests(read_reqs=read_reqs)
         sync_execute_read_reqs(
