@@ -7,8 +7,28 @@ import tsb200_loader; tsb200_loader.load()
 import bench
 from torchsnapshot_b200 import scheduler
 from torchsnapshot_b200.snapshot import Snapshot, StateDict
-state=bench.build_state("cuda:0"); P=bench.payload_bytes(state)
+def build_c3(device, total=8e9, seed=1234):
+    """BASELINE config 2: ~20k tensors of 4 KB-4 MB log-uniform, 10% bf16, 5% int64, 1% strided, 1% 0-d."""
+    import numpy as np
+    rs = np.random.RandomState(seed); st = {}; tot = 0; i = 0
+    g = torch.Generator(device=device).manual_seed(seed)
+    while tot < total:
+        n = 4 * int(round(2 ** rs.uniform(10, 20))); kind = rs.uniform()
+        if kind < 0.10: t = torch.empty(n // 2, dtype=torch.bfloat16, device=device); t.view(torch.int16).random_(-30000, 30000, generator=g)
+        elif kind < 0.15: t = torch.empty(max(n // 8, 1), dtype=torch.int64, device=device); t.random_(generator=g)
+        elif kind < 0.16:
+            b = torch.empty((max(n // 512, 1), 128), dtype=torch.float32, device=device); b.view(torch.int32).random_(generator=g); t = b[:, ::2]
+        elif kind < 0.17: t = torch.tensor(float(i), device=device)
+        else: t = torch.empty(n // 4, dtype=torch.float32, device=device); t.view(torch.int32).random_(generator=g)
+        st[f"t{i}"] = t; tot += t.numel() * t.element_size(); i += 1
+    return st
+if os.environ.get("WORKLOAD") == "c3": state = build_c3("cuda:0")
+else: state=bench.build_state("cuda:0")
+P=bench.payload_bytes(state); print("tensors", len(state), "payload GB", P/1e9)
 outs=StateDict({k: torch.empty_like(v) for k,v in state.items()})
+def blocked():
+    d=tempfile.mkdtemp(dir="/dev/shm"); torch.cuda.synchronize(); t0=time.monotonic()
+    p=Snapshot.async_take(d, app, replicated=["**"]); b=(time.monotonic()-t0)*1e3; p.wait(); shutil.rmtree(d); return round(b,1)
 app={"ddp": StateDict(state)}
 NT=int(os.environ.get('TRIALS','4'))
 for trial in range(NT):
@@ -34,3 +54,4 @@ for trial in range(NT):
     if prof:
         s=io.StringIO(); pstats.Stats(prof,stream=s).sort_stats("cumulative").print_stats(25); print(s.getvalue()[:3500])
     shutil.rmtree(d)
+    print(json.dumps({"trial":trial,"async_take_blocked_ms":blocked()}),flush=True)

@@ -12,7 +12,9 @@ from .manifest import DictEntry, Entry, ListEntry, Manifest, OrderedDictEntry
 
 
 def _encode(s: str) -> str:
-    return s.replace("%", "%25").replace("/", "%2F")
+    if "%" in s or "/" in s:
+        return s.replace("%", "%25").replace("/", "%2F")
+    return s
 
 
 def _decode(s: str) -> str:
@@ -20,9 +22,14 @@ def _decode(s: str) -> str:
 
 
 def _flattenable_dict(d: Dict[Any, Any]) -> bool:
-    if not all(isinstance(k, (str, int)) for k in d):
-        return False
-    return len({str(k) for k in d}) == len(d)
+    all_str = True
+    for k in d:
+        if type(k) is not str:
+            all_str = False
+            if not isinstance(k, (str, int)):
+                return False
+    # distinct str keys cannot collide; mixed int/str keys may ("1" vs 1)
+    return all_str or len({str(k) for k in d}) == len(d)
 
 
 def flatten(obj: Any, prefix: str) -> Tuple[Manifest, Dict[str, Any]]:

@@ -40,6 +40,8 @@ from .manifest import (
 )
 from .regions import RegionTuple, box_regions, contiguous_strides, pack_regions, unpack_regions
 from .serialization import (
+    _BUFFER_PROTOCOL_SET as _BUFFER_PROTOCOL_DTYPES,
+    _DTYPE_TO_STRING as _DTYPE_STRINGS,
     Serializer,
     SUPPORTED_QUANTIZED_DTYPES,
     dtype_to_element_size,
@@ -51,6 +53,10 @@ from .serialization import (
 logger: logging.Logger = logging.getLogger(__name__)
 
 TensorPrepareFunc = Callable[[torch.Tensor, bool], torch.Tensor]
+
+# hot-loop constants (prepare_write runs once per tensor: 20k times at BASELINE config 2)
+_BUFFER_PROTOCOL = Serializer.BUFFER_PROTOCOL.value
+_TORCH_SAVE = Serializer.TORCH_SAVE.value
 
 try:  # ShardedTensor is optional at import time; only sharded state needs it
     from torch.distributed._shard.sharded_tensor import ShardedTensor
@@ -228,26 +234,28 @@ class TensorIOPreparer:
         is_async_snapshot: bool = False,
         _tensor_prepare_func: Optional[TensorPrepareFunc] = None,
     ) -> Tuple[TensorEntry, List[WriteReq]]:
-        proc = tensor if _tensor_prepare_func is None else _tensor_prepare_func(tensor, True)
-        if proc.shape != tensor.shape:
-            raise RuntimeError(
-                "_tensor_prepare_func shouldn't change the tensor's shape "
-                f"(changed from {tensor.shape} to {proc.shape})."
-            )
-        serializer = (
-            Serializer.BUFFER_PROTOCOL.value if is_buffer_protocol_dtype(proc.dtype) else Serializer.TORCH_SAVE.value
-        )
+        if _tensor_prepare_func is None:
+            dtype = tensor.dtype
+        else:
+            proc = _tensor_prepare_func(tensor, True)
+            if proc.shape != tensor.shape:
+                raise RuntimeError(
+                    "_tensor_prepare_func shouldn't change the tensor's shape "
+                    f"(changed from {tensor.shape} to {proc.shape})."
+                )
+            dtype = proc.dtype
+        dtype_str = _DTYPE_STRINGS.get(dtype)
+        if dtype_str is None:
+            dtype_str = dtype_to_string(dtype)  # raises for unsupported dtypes
         entry = TensorEntry(
-            location=storage_path,
-            serializer=serializer,
-            dtype=dtype_to_string(proc.dtype),
-            shape=list(proc.shape),
-            replicated=False,
+            storage_path,
+            _BUFFER_PROTOCOL if dtype in _BUFFER_PROTOCOL_DTYPES else _TORCH_SAVE,
+            dtype_str,
+            list(tensor.shape),
+            False,
         )
-        stager = TensorBufferStager(
-            tensor=tensor, entry=entry, is_async_snapshot=is_async_snapshot, _tensor_prepare_func=_tensor_prepare_func
-        )
-        return entry, [WriteReq(path=storage_path, buffer_stager=stager)]
+        stager = TensorBufferStager(tensor, entry, is_async_snapshot, _tensor_prepare_func)
+        return entry, [WriteReq(storage_path, stager)]
 
     @classmethod
     def prepare_read(
@@ -679,10 +687,10 @@ class PrimitivePreparer:
 # ----------------------------------------------------------------------------------------------
 def get_storage_path(obj: Any, logical_path: str, rank: int, replicated: bool) -> str:
     if _is_sharded_tensor(obj):
-        return os.path.join("sharded", logical_path)
+        return "sharded/" + logical_path
     if replicated:
-        return os.path.join("replicated", logical_path)
-    return os.path.join(str(rank), logical_path)
+        return "replicated/" + logical_path
+    return f"{rank}/{logical_path}"
 
 
 def prepare_write(
@@ -692,7 +700,27 @@ def prepare_write(
     replicated: bool,
     is_async_snapshot: bool = False,
     _tensor_prepare_func: Optional[TensorPrepareFunc] = None,
+    max_chunk_size_bytes: Optional[int] = None,
 ) -> Tuple[Entry, List[WriteReq]]:
+    """Entry + write requests of one leaf (reference io_preparer.py:73-128).  `max_chunk_size_bytes`
+    lets a caller that plans thousands of leaves read the environment knob once."""
+    if type(obj) is torch.Tensor or type(obj) is torch.nn.Parameter:
+        # the overwhelmingly common leaf: skip the primitive / sharded dispatch
+        if max_chunk_size_bytes is None:
+            max_chunk_size_bytes = knobs.get_max_chunk_size_bytes()
+        storage_path = ("replicated/" if replicated else f"{rank}/") + logical_path
+        if obj.numel() * obj.element_size() > max_chunk_size_bytes:
+            entry, wrs = ChunkedTensorIOPreparer.prepare_write(
+                storage_path=storage_path,
+                tensor=obj,
+                chunking_instruction=ChunkedTensorIOPreparer.chunk_tensor(obj, chunk_sz_bytes=max_chunk_size_bytes),
+                is_async_snapshot=is_async_snapshot,
+                _tensor_prepare_func=_tensor_prepare_func,
+            )
+        else:
+            entry, wrs = TensorIOPreparer.prepare_write(storage_path, obj, is_async_snapshot, _tensor_prepare_func)
+        entry.replicated = replicated
+        return entry, wrs
     if PrimitivePreparer.should_inline(obj):
         entry = PrimitivePreparer.prepare_write(obj)
         entry.replicated = replicated
@@ -704,11 +732,13 @@ def prepare_write(
             _tensor_prepare_func=_tensor_prepare_func,
         )
     if isinstance(obj, torch.Tensor):
-        if obj.numel() * obj.element_size() > knobs.get_max_chunk_size_bytes():
+        if max_chunk_size_bytes is None:
+            max_chunk_size_bytes = knobs.get_max_chunk_size_bytes()
+        if obj.numel() * obj.element_size() > max_chunk_size_bytes:
             entry, wrs = ChunkedTensorIOPreparer.prepare_write(
                 storage_path=storage_path,
                 tensor=obj,
-                chunking_instruction=ChunkedTensorIOPreparer.chunk_tensor(obj),
+                chunking_instruction=ChunkedTensorIOPreparer.chunk_tensor(obj, chunk_sz_bytes=max_chunk_size_bytes),
                 is_async_snapshot=is_async_snapshot,
                 _tensor_prepare_func=_tensor_prepare_func,
             )

@@ -167,6 +167,69 @@ class PrimitiveEntry(Entry):
 
 Manifest = Dict[str, Entry]
 
+_esc = json.encoder.encode_basestring_ascii  # C implementation; same escaping as json.dumps
+
+
+def _scalar_list_text(vals: Any, pad: str) -> str:
+    """A JSON array of scalars laid out the way json.dumps(indent=2) does: one element per line."""
+    if vals is None:
+        return "null"
+    if not vals:
+        return "[]"
+    inner = pad + "  "
+    return "[\n" + ",\n".join(inner + (str(v) if type(v) is int else json.dumps(v)) for v in vals) + "\n" + pad + "]"
+
+
+def _tensor_text(e: "TensorEntry", pad: str) -> str:
+    p = pad + "  "
+    return (
+        "{\n"
+        f'{p}"type": "Tensor",\n'
+        f'{p}"location": {_esc(e.location)},\n'
+        f'{p}"serializer": {_esc(e.serializer)},\n'
+        f'{p}"dtype": {_esc(e.dtype)},\n'
+        f'{p}"shape": {_scalar_list_text(e.shape, p)},\n'
+        f'{p}"replicated": {"true" if e.replicated else "false"},\n'
+        f'{p}"byte_range": {_scalar_list_text(e.byte_range, p)}\n'
+        f"{pad}}}"
+    )
+
+
+def _shards_text(shards: List["Shard"], pad: str) -> str:
+    if not shards:
+        return "[]"
+    p, q = pad + "  ", pad + "    "
+    items = [
+        "{\n"
+        f'{q}"offsets": {_scalar_list_text(s.offsets, q)},\n'
+        f'{q}"sizes": {_scalar_list_text(s.sizes, q)},\n'
+        f'{q}"tensor": {_tensor_text(s.tensor, q)}\n'
+        f"{p}}}"
+        for s in shards
+    ]
+    return "[\n" + ",\n".join(p + it for it in items) + "\n" + pad + "]"
+
+
+def _entry_text(entry: Entry, pad: str) -> str:
+    kind = type(entry)
+    if kind is TensorEntry:
+        return _tensor_text(entry, pad)
+    p = pad + "  "
+    if kind is ShardedTensorEntry:
+        return "{\n" f'{p}"type": "ShardedTensor",\n{p}"shards": {_shards_text(entry.shards, p)}\n{pad}}}'
+    if kind is ChunkedTensorEntry:
+        return (
+            "{\n"
+            f'{p}"type": "ChunkedTensor",\n'
+            f'{p}"dtype": {_esc(entry.dtype)},\n'
+            f'{p}"shape": {_scalar_list_text(entry.shape, p)},\n'
+            f'{p}"chunks": {_shards_text(entry.chunks, p)},\n'
+            f'{p}"replicated": {"true" if entry.replicated else "false"}\n'
+            f"{pad}}}"
+        )
+    # containers, objects, primitives: few per snapshot; the generic encoder, re-indented
+    return json.dumps(entry.to_obj(), sort_keys=False, indent=2).replace("\n", "\n" + pad)
+
 
 def _tensor_from_obj(o: Dict[str, Any]) -> TensorEntry:
     return TensorEntry(
@@ -216,12 +279,20 @@ class SnapshotMetadata:
     manifest: Manifest
 
     def to_yaml(self) -> str:
-        doc = {
-            "version": self.version,
-            "world_size": self.world_size,
-            "manifest": {path: entry.to_obj() for path, entry in self.manifest.items()},
-        }
-        return json.dumps(doc, sort_keys=False, indent=2)
+        """The `.snapshot_metadata` text: character for character what the reference's
+        `json.dumps(asdict(self), sort_keys=False, indent=2)` gives (manifest.py:283-289), produced by a
+        schema-aware writer because the generic encoder with `indent` runs in pure Python (0.45 s for
+        13 k entries, on the critical path of a take)."""
+        pad = "    "
+        parts = [f"{pad}{_esc(path)}: {_entry_text(entry, pad)}" for path, entry in self.manifest.items()]
+        manifest = "{\n" + ",\n".join(parts) + "\n  }" if parts else "{}"
+        return (
+            "{\n"
+            f'  "version": {_esc(self.version)},\n'
+            f'  "world_size": {json.dumps(self.world_size)},\n'
+            f'  "manifest": {manifest}\n'
+            "}"
+        )
 
     @classmethod
     def from_yaml(cls, text: str) -> "SnapshotMetadata":

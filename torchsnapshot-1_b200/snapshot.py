@@ -257,14 +257,16 @@ class Snapshot:
         object_entries: Dict[str, Entry] = {}
         write_reqs_by_path: Dict[str, List[WriteReq]] = {}
         primitive_entries: Dict[str, Entry] = {}
+        max_chunk = knobs.get_max_chunk_size_bytes()
         for logical_path, obj in flattened.items():
             entry, wrs = prepare_write(
-                obj=obj,
-                logical_path=logical_path,
-                rank=rank,
-                replicated=logical_path in replicated_paths,
-                is_async_snapshot=is_async,
-                _tensor_prepare_func=functools.partial(prepare_func, logical_path) if prepare_func else None,
+                obj,
+                logical_path,
+                rank,
+                logical_path in replicated_paths,
+                is_async,
+                functools.partial(prepare_func, logical_path) if prepare_func else None,
+                max_chunk,
             )
             if isinstance(entry, PrimitiveEntry):
                 primitive_entries[logical_path] = entry
