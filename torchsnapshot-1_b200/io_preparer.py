@@ -18,6 +18,7 @@ import itertools
 import logging
 import math
 import os
+import warnings
 from collections import defaultdict
 from concurrent.futures import Executor
 from dataclasses import dataclass
@@ -42,6 +43,7 @@ from .regions import RegionTuple, box_regions, contiguous_strides, pack_regions,
 from .serialization import (
     _BUFFER_PROTOCOL_SET as _BUFFER_PROTOCOL_DTYPES,
     _DTYPE_TO_STRING as _DTYPE_STRINGS,
+    _STRING_TO_DTYPE as _STRING_DTYPES,
     Serializer,
     SUPPORTED_QUANTIZED_DTYPES,
     dtype_to_element_size,
@@ -93,14 +95,14 @@ def tensor_as_memoryview(tensor: torch.Tensor) -> memoryview:
     return memoryview(flat.view(torch.uint8).numpy()).cast("b")
 
 
-def tensor_from_memoryview(mv: BufferType, dtype: torch.dtype, shape: Sequence[int]) -> torch.Tensor:
-    import warnings
+# tensors made from read-only buffers are intermediate, read-only views (reference serialization.py:236-244)
+warnings.filterwarnings("ignore", message="The given buffer is not writable")
 
+
+def tensor_from_memoryview(mv: BufferType, dtype: torch.dtype, shape: Sequence[int]) -> torch.Tensor:
     if len(mv) == 0:
         return torch.empty(list(shape), dtype=dtype)
-    with warnings.catch_warnings():
-        warnings.simplefilter("ignore")
-        return torch.frombuffer(mv, dtype=dtype).reshape(list(shape))
+    return torch.frombuffer(mv, dtype=dtype).reshape(list(shape))
 
 
 def tensor_copy(dst: torch.Tensor, src: torch.Tensor) -> None:
@@ -215,7 +217,12 @@ class TensorBufferConsumer(BufferConsumer):
             await consume_device_buffer(self, buf, self.tensor.device.index, executor)
             return
         loaded = self.deserialize_tensor(buf=buf, entry=self.entry)
-        await _run_in_executor(executor, tensor_copy, self.tensor, loaded)
+        if executor is None or (len(buf) < _INLINE_COPY_BYTES and not self.tensor.is_cuda):
+            # a thread hop costs more than copying a small host tensor (the reference hops per tensor,
+            # tensor.py:329-338: 4 s for 20 k tensors)
+            tensor_copy(self.tensor, loaded)
+        else:
+            await _run_in_executor(executor, tensor_copy, self.tensor, loaded)
 
     def get_consuming_cost_bytes(self) -> int:
         n = TensorIOPreparer.get_tensor_size_from_entry(self.entry)
@@ -224,6 +231,9 @@ class TensorBufferConsumer(BufferConsumer):
         if self.entry.serializer == Serializer.BUFFER_PROTOCOL.value:
             return n
         raise ValueError(f"Unrecognized serializer: {self.entry.serializer}.")
+
+
+_INLINE_COPY_BYTES = 256 * 1024
 
 
 class TensorIOPreparer:
@@ -264,13 +274,18 @@ class TensorIOPreparer:
         tensor_out: Optional[torch.Tensor] = None,
         buffer_size_limit_bytes: Optional[int] = None,
     ) -> Tuple[List[ReadReq], Future]:
-        if tensor_out is None or not cls.can_load_inplace(entry=entry, obj=tensor_out):
+        if (
+            tensor_out is None
+            or not isinstance(tensor_out, torch.Tensor)
+            or _STRING_DTYPES.get(entry.dtype) != tensor_out.dtype
+            or entry.shape != list(tensor_out.shape)
+        ):
             tensor_out = cls.empty_tensor_from_entry(entry)
         if buffer_size_limit_bytes is not None and entry.serializer == Serializer.BUFFER_PROTOCOL.value:
             return cls.prepare_read_tiled(entry, tensor_out, buffer_size_limit_bytes)
-        consumer = TensorBufferConsumer(tensor=tensor_out, entry=entry)
-        return [ReadReq(path=entry.location, byte_range=entry.byte_range_tuple, buffer_consumer=consumer)], Future(
-            obj=tensor_out
+        br = entry.byte_range
+        return [ReadReq(entry.location, TensorBufferConsumer(tensor_out, entry), None if br is None else (br[0], br[1]))], Future(
+            tensor_out
         )
 
     @classmethod
