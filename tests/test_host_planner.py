@@ -260,3 +260,16 @@ def test_chunks_are_spread_in_offset_order():
     sizes = [sum(100 if p == "big" else 10 for p, _ in r) for r in got]
     assert max(sizes) - min(sizes) <= 100
     assert sorted(i for r in got for p, i in r if p == "big") == list(range(6))
+
+
+def test_speed_weighted_partition_balances_finish_time():
+    loads = [(f"p{i}", 0, 100, False) for i in range(40)]
+    even = assign_write_loads(loads, [0, 0, 0, 0])
+    assert [len(r) for r in even] == [10, 10, 10, 10]
+    weighted = assign_write_loads(loads, [0, 0, 0, 0], [26.5, 38.0, 38.0, 38.0])
+    counts = [len(r) for r in weighted]
+    assert sum(counts) == 40 and counts[0] < counts[1] and max(counts) - min(counts) <= 4
+    finish = [c * 100 / s for c, s in zip(counts, [26.5, 38.0, 38.0, 38.0])]
+    assert max(finish) < 10 * 100 / 26.5  # better than the byte-balanced plan on these links
+    # unusable speed vectors fall back to byte balance
+    assert assign_write_loads(loads, [0, 0, 0, 0], [1.0, None, 1.0, 1.0]) == even

@@ -11,7 +11,7 @@ one all_gather_object instead of rank 0 computing and broadcasting it (one colle
 import copy
 import os
 from collections import defaultdict
-from typing import Any, Dict, List, Sequence, Tuple
+from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 from .io_types import WriteReq
 from .manifest import ChunkedTensorEntry, Entry, is_replicated
@@ -28,15 +28,28 @@ def _write_req_size(wr: WriteReq) -> int:
 
 
 def assign_write_loads(
-    loads: Sequence[Tuple[str, int, int, bool]], rank_to_size: Sequence[int]
+    loads: Sequence[Tuple[str, int, int, bool]],
+    rank_to_size: Sequence[int],
+    rank_to_speed: Optional[Sequence[float]] = None,
 ) -> List[List[Tuple[str, int]]]:
     """loads: (logical_path, write_req_idx, size, subpartitionable) in rank-0 order.  Returns, per
-    rank, the (logical_path, write_req_idx) pairs it writes."""
+    rank, the (logical_path, write_req_idx) pairs it writes.
+
+    `rank_to_speed` (relative device->host throughput of every rank, see `observed_speed`) turns
+    "fewest bytes" into "earliest finish": when N GPUs copy to the host at once their links are not
+    equally fast (profiles/r01_multi_gpu_peaks.json: 26.5 vs ~38 GB/s at N=4), and the take ends when
+    the slowest rank ends.  Without speeds this is the reference's byte balance (partitioner.py:42-79)."""
     sizes = list(rank_to_size)
     out: List[List[Tuple[str, int]]] = [[] for _ in sizes]
+    if rank_to_speed is None or len(rank_to_speed) != len(sizes) or any(not s or s <= 0 for s in rank_to_speed):
+        speed = [1.0] * len(sizes)
+    else:
+        mean = sum(rank_to_speed) / len(rank_to_speed)
+        # clamp: a noisy estimate must not starve or overload a rank
+        speed = [min(max(s / mean, 0.5), 2.0) for s in rank_to_speed]
 
     def lightest() -> int:
-        return min(range(len(sizes)), key=lambda r: (sizes[r], r))
+        return min(range(len(sizes)), key=lambda r: (sizes[r] / speed[r], r))
 
     # whole logical paths first, then the chunks of sub-partitionable paths (reference order)
     grouped: Dict[str, List[Tuple[int, int]]] = defaultdict(list)
@@ -59,6 +72,23 @@ def assign_write_loads(
         out[r].append((path, idx))
         sizes[r] += size
     return out
+
+
+_speed_estimate: Optional[float] = None  # this rank's device->host GB/s under load (EMA over takes)
+
+
+def observed_speed() -> Optional[float]:
+    """This rank's device->host throughput as measured on its previous takes (None before the first)."""
+    return _speed_estimate
+
+
+def record_take_speed(nbytes: int, device_ms: float) -> None:
+    """Called by the scheduler when a take has drained: bytes moved / device time of pack + D2H."""
+    global _speed_estimate
+    if nbytes < (64 << 20) or device_ms <= 0:
+        return  # too small to say anything about the link
+    gbps = nbytes / device_ms / 1e6
+    _speed_estimate = gbps if _speed_estimate is None else 0.5 * _speed_estimate + 0.5 * gbps
 
 
 def partition_write_reqs(
@@ -88,14 +118,15 @@ def partition_write_reqs(
         for idx, wr in enumerate(write_reqs.get(path, [])):
             loads.append((path, idx, _write_req_size(wr), sub))
     gathered: List[Any] = [None] * world
-    pg.all_gather_object(gathered, (non_replicated_size, loads))
+    pg.all_gather_object(gathered, (non_replicated_size, loads, observed_speed()))
     # rank 0's view defines the units, like the reference; a chunked entry is only split when every
     # rank chunked it identically
     base_loads = gathered[0][1]
     same = all(g[1] == base_loads for g in gathered)
     if not same:
         base_loads = [(p, i, s, False) for p, i, s, _sub in base_loads]
-    mine = sorted(assign_write_loads(base_loads, [g[0] for g in gathered])[rank])
+    speeds = [g[2] for g in gathered]
+    mine = sorted(assign_write_loads(base_loads, [g[0] for g in gathered], speeds if all(speeds) else None)[rank])
     new_entries: Dict[str, Entry] = {k: v for k, v in entries.items() if k not in replicated}
     new_wrs: Dict[str, List[WriteReq]] = {k: v for k, v in write_reqs.items() if k not in replicated}
     for path, idx in mine:

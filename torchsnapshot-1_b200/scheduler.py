@@ -235,6 +235,12 @@ class PendingIOWork:
         finally:
             self.executor.shutdown(wait=False)
         self.stats.writes_done = time.monotonic()
+        try:  # feed the replicated-write partitioner with this rank's measured device->host speed
+            from .partitioner import record_take_speed
+
+            record_take_speed(self.stats.pack_kernel_bytes() // 2, self.stats.device_ms())
+        except Exception:  # pragma: no cover - statistics only
+            pass
         elapsed = max(self.stats.writes_done - self.stats.begin, 1e-9)
         logger.info(
             f"Rank {self.rank} completed writing in {elapsed:.3f} s "
