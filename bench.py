@@ -210,6 +210,9 @@ def main():
     from torchsnapshot_b200.pg_wrapper import PGWrapper
     from torchsnapshot_b200.snapshot import Snapshot, StateDict
 
+    # stdout carries exactly one JSON line: keep NCCL's version banner out of it
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -20,6 +20,7 @@ over storage -> PCIe once and then over NVLink.  The result is bit-identical to 
 
 import asyncio
 import logging
+import time
 from concurrent.futures import ThreadPoolExecutor
 from dataclasses import dataclass
 from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
@@ -138,6 +139,7 @@ class ReshardStats:
         self.copy_ms = 0.0  # device time of the copy kernels (CUDA events)
         self.launches = 0
         self.skipped: List[str] = []  # sharded paths some rank did not offer: load them the ordinary way
+        self.phase_ms: Dict[str, float] = {}  # wall-clock phases: plan, read, exchange, copy, barrier
 
 
 last_stats: Optional[ReshardStats] = None
@@ -242,6 +244,7 @@ def p2p_restore_units(
     from .scheduler import _Allocator, _read_into_pinned  # shared read machinery
 
     stats = ReshardStats()
+    t_begin = time.monotonic()
     rank, world = pg.get_rank(), pg.get_world_size()
     mine_by_key = {u.key: u for u in units}
     gathered: List[Any] = [None] * world
@@ -257,81 +260,111 @@ def p2p_restore_units(
     for d in gathered:
         for k, (_need, nbytes) in d.items():
             sizes[k] = max(sizes.get(k, 0), nbytes)
-    owned = [k for k, o in owners.items() if o == rank]
+    owned = sorted(k for k, o in owners.items() if o == rank)
     staged: Dict[UnitKey, int] = {}
-
-    async def read_all() -> None:
-        loop = asyncio.get_running_loop()
-        executor = ThreadPoolExecutor(max_workers=4, thread_name_prefix="tsb-reshard")
-        alloc = _Allocator()
-        sem = asyncio.Semaphore(32)
-
-        async def one(key: UnitKey) -> None:
-            nbytes = sizes[key]
-            br = None if key[1] < 0 else (key[1], key[2])
-            async with sem:
-                dptr = await alloc.device(eng, nbytes)
-                staged[key] = dptr
-                pbuf = await alloc.pinned(eng, nbytes)
-                try:
-                    rr = ReadReq(path=key[0], buffer_consumer=None, byte_range=br)  # type: ignore[arg-type]
-                    await _read_into_pinned(loop, executor, storage, rr, pbuf, nbytes)
-                    ctx.memcpy_h2d(STREAM_H2D, dptr, pbuf.ptr, nbytes)
-                    ev = ctx.event_record(STREAM_H2D)
-                    try:
-                        await loop.run_in_executor(executor, ctx.event_sync, ev)
-                    finally:
-                        ctx.event_release(ev)
-                finally:
-                    pbuf.release()
-                    alloc.notify()
-            stats.read_bytes += nbytes
-
-        try:
-            await asyncio.gather(*(one(k) for k in owned))
-        finally:
-            executor.shutdown(wait=False)
-
+    blocks: List[int] = []  # device arena blocks to free at the end
+    opened: Dict[Tuple[int, bytes], int] = {}
+    executor = ThreadPoolExecutor(max_workers=4, thread_name_prefix="tsb-reshard")
     try:
-        event_loop.run_until_complete(read_all())
-        # publish where every unit lives (IPC handle of its arena segment + offset); the all-gather also
-        # tells everybody that all units are resident
+        # ---- staging for the units this rank owns: ONE block when the arena allows it, so that every
+        # peer maps a single IPC handle (cudaIpcOpenMemHandle costs milliseconds per handle) ----------
+        total_owned = sum((sizes[k] + 511) // 512 * 512 for k in owned)
+        if owned:
+            try:
+                base = ctx.dev_alloc(total_owned)
+                blocks.append(base)
+                off = 0
+                for k in owned:
+                    staged[k] = base + off
+                    off += (sizes[k] + 511) // 512 * 512
+            except Exception:  # larger than one arena segment can be: one block per unit
+                for k in owned:
+                    staged[k] = ctx.dev_alloc(sizes[k])
+                    blocks.append(staged[k])
+        # ---- addresses are known before any byte is read: publish them now (IPC handle + offset) ---
         exports = {k: ctx.ipc_export(dptr) for k, dptr in staged.items()}
         all_exports: List[Any] = [None] * world
         pg.all_gather_object(all_exports, exports)
-        opened: Dict[Tuple[int, bytes], int] = {}
+        t_read = time.monotonic()
+        stats.phase_ms["plan"] = 1e3 * (t_read - t_begin)
         regions: List[RegionTuple] = []
-        try:
+
+        async def build_regions() -> None:
+            n = 0
             for key, unit in mine_by_key.items():
                 owner = owners.get(key)
                 if owner is None or unit.need == 0:
                     continue
                 if owner == rank:
-                    base = staged[key]
+                    src_base = staged[key]
                     stats.local_bytes += unit.need
                 else:
                     handle, offset = all_exports[owner][key]
                     hk = (owner, handle)
                     if hk not in opened:
                         opened[hk] = ctx.ipc_open(handle)
-                    base = opened[hk] + offset
+                    src_base = opened[hk] + offset
                     stats.peer_bytes += unit.need
-                regions += unit.regions(base)
-            arr = regions_to_array(regions)
-            if arr.shape[0]:
-                eng.wait_current_stream(STREAM_PACK)
-                k0, k1 = eng.copy_region_array_timed(arr, STREAM_PACK)
-                ctx.stream_sync(STREAM_PACK)
-                stats.copy_ms += ctx.event_elapsed_ms(k0, k1)
-                stats.launches += 1
-                ctx.event_release(k0)
-                ctx.event_release(k1)
-            pg.barrier()  # nobody may free its staging while a peer still reads it
-        finally:
-            for base_addr in opened.values():
-                ctx.ipc_close(base_addr)
+                regions.extend(unit.regions(src_base))
+                n += 1
+                if n % 8 == 0:
+                    await asyncio.sleep(0)  # let the read pipeline dispatch
+
+        async def read_all() -> None:
+            loop = asyncio.get_running_loop()
+            alloc = _Allocator()
+            sem = asyncio.Semaphore(32)
+
+            async def one(key: UnitKey) -> None:
+                nbytes = sizes[key]
+                br = None if key[1] < 0 else (key[1], key[2])
+                async with sem:
+                    pbuf = await alloc.pinned(eng, nbytes)
+                    try:
+                        rr = ReadReq(path=key[0], buffer_consumer=None, byte_range=br)  # type: ignore[arg-type]
+                        await _read_into_pinned(loop, executor, storage, rr, pbuf, nbytes)
+                        ctx.memcpy_h2d(STREAM_H2D, staged[key], pbuf.ptr, nbytes)
+                        ev = ctx.event_record(STREAM_H2D)
+                        try:
+                            await loop.run_in_executor(executor, ctx.event_sync, ev)
+                        finally:
+                            ctx.event_release(ev)
+                    finally:
+                        pbuf.release()
+                        alloc.notify()
+                stats.read_bytes += nbytes
+
+            # the copy regions are built while the reads are in flight
+            await asyncio.gather(build_regions(), *(one(k) for k in owned))
+
+        event_loop.run_until_complete(read_all())
+        t_bar = time.monotonic()
+        stats.phase_ms["read"] = 1e3 * (t_bar - t_read)
+        pg.barrier()  # every owner's units are resident in its staging block
+        t_copy = time.monotonic()
+        stats.phase_ms["exchange"] = 1e3 * (t_copy - t_bar)
+        # ---- ONE launch: own staging + peers' staging (over NVLink) -> this rank's tensors ---------------
+        arr = regions_to_array(regions)
+        if arr.shape[0]:
+            eng.wait_current_stream(STREAM_PACK)
+            k0, k1 = eng.copy_region_array_timed(arr, STREAM_PACK)
+            ctx.stream_sync(STREAM_PACK)
+            stats.copy_ms += ctx.event_elapsed_ms(k0, k1)
+            stats.launches += 1
+            ctx.event_release(k0)
+            ctx.event_release(k1)
+        t_end = time.monotonic()
+        stats.phase_ms["copy"] = 1e3 * (t_end - t_copy)
+        pg.barrier()  # nobody may free its staging while a peer still reads it
+        stats.phase_ms["barrier"] = 1e3 * (time.monotonic() - t_end)
     finally:
-        for dptr in staged.values():
+        executor.shutdown(wait=False)
+        for base_addr in opened.values():
+            try:
+                ctx.ipc_close(base_addr)
+            except Exception:  # pragma: no cover
+                pass
+        for dptr in blocks:
             ctx.dev_free(dptr)
     return stats
 
