@@ -53,5 +53,12 @@ for trial in range(NT):
     print(json.dumps({"trial":trial,"restore_ms":round(1e3*(t1-t0),1),"GBps":round(P/(t1-t0)/1e9,2),"read_begin":round(1e3*(rs.begin-t0),1),"unpack_ms":round(rs.unpack_ms,2)}),flush=True)
     if prof:
         s=io.StringIO(); pstats.Stats(prof,stream=s).sort_stats("cumulative").print_stats(25); print(s.getvalue()[:3500])
+    if rs.trace and trial==NT-1:
+        tr=sorted(rs.trace, key=lambda x:x[1])
+        import statistics
+        rd=[(r-p)*1e3 for q,s_,p,r,e,n in tr]; dv=[(e-r)*1e3 for q,s_,p,r,e,n in tr]
+        print("reads: n",len(tr),"read_ms med",round(statistics.median(rd),1),"max",round(max(rd),1),"device_phase_ms med",round(statistics.median(dv),1),"max",round(max(dv),1))
+        print("first read start",round(tr[0][2]*1e3,1),"last read end",round(max(x[3] for x in tr)*1e3,1),"last done",round(max(x[4] for x in tr)*1e3,1))
+        for x in tr[:3]+tr[30:33]+tr[-3:]: print("  q %.1f slot %.1f pinned %.1f read_done %.1f done %.1f MB %.0f" % tuple([1e3*v for v in x[:5]]+[x[5]/1e6]))
     shutil.rmtree(d)
     print(json.dumps({"trial":trial,"async_take_blocked_ms":blocked()}),flush=True)

@@ -318,11 +318,15 @@ def p2p_restore_units(
             async def one(key: UnitKey) -> None:
                 nbytes = sizes[key]
                 br = None if key[1] < 0 else (key[1], key[2])
-                async with sem:
+                await sem.acquire()  # the slot covers the storage read only, not the H2D that follows
+                held = True
+                try:
                     pbuf = await alloc.pinned(eng, nbytes)
                     try:
                         rr = ReadReq(path=key[0], buffer_consumer=None, byte_range=br)  # type: ignore[arg-type]
                         await _read_into_pinned(loop, executor, storage, rr, pbuf, nbytes)
+                        sem.release()
+                        held = False
                         ctx.memcpy_h2d(STREAM_H2D, staged[key], pbuf.ptr, nbytes)
                         ev = ctx.event_record(STREAM_H2D)
                         try:
@@ -332,6 +336,9 @@ def p2p_restore_units(
                     finally:
                         pbuf.release()
                         alloc.notify()
+                finally:
+                    if held:
+                        sem.release()
                 stats.read_bytes += nbytes
 
             # the copy regions are built while the reads are in flight

@@ -42,10 +42,11 @@ logger: logging.Logger = logging.getLogger(__name__)
 
 _MAX_PER_RANK_MEMORY_BUDGET_BYTES: int = 32 * 1024 * 1024 * 1024
 _AVAILABLE_MEMORY_MULTIPLIER: float = 0.6
-_MAX_PER_RANK_CPU_CONCURRENCY: int = 4
+_MAX_PER_RANK_CPU_CONCURRENCY: int = int(os.environ.get("TSB200_CPU_CONCURRENCY", "4"))
 # storage operations in flight per rank.  The reference uses 16 (scheduler.py:30); 32 single-threaded
 # writers measured best on the B200 box (tmpfs: 28.8 vs 26.6 GB/s end-to-end take), TSB200_IO_CONCURRENCY overrides.
 _MAX_PER_RANK_IO_CONCURRENCY: int = int(os.environ.get("TSB200_IO_CONCURRENCY", "32"))
+_TRACE_READS = os.environ.get("TSB200_TRACE_READS") == "1"
 _STAGING_ALIGN = 512  # each file's bytes start 512-B aligned inside the device staging block
 
 
@@ -156,6 +157,7 @@ class _ReadStats:
         self.device_bytes = 0  # bytes that went pinned -> H2D -> unpack kernel
         self.unpack_ms = 0.0  # device time of the unpack kernels (CUDA events)
         self.unpack_launches = 0
+        self.trace: List[Tuple[float, float, float, float, float, int]] = []  # per device read (TSB200_TRACE_READS=1)
 
 
 last_read_stats: Optional[_ReadStats] = None
@@ -467,10 +469,20 @@ async def execute_read_reqs(
         nbytes = rr.byte_range[1] - rr.byte_range[0] if rr.byte_range is not None else consumer.consumed_nbytes()
         if nbytes == 0:
             return
-        async with io_slots:
+        t_q = time.monotonic()
+        # the I/O slot covers the storage read only: the device phase (H2D + unpack) of one request must
+        # not keep the next read from starting (it is bounded by the pinned / device arenas instead)
+        await io_slots.acquire()
+        slot_held = True
+        try:
+            t_s = time.monotonic()
             pbuf = await alloc.pinned(eng, nbytes)
             try:
+                t_p = time.monotonic()
                 await _read_into_pinned(loop, executor, storage, rr, pbuf, nbytes)
+                io_slots.release()
+                slot_held = False
+                t_r = time.monotonic()
                 dptr = await alloc.device(eng, nbytes)
                 try:
                     ctx.memcpy_h2d(STREAM_H2D, dptr, pbuf.ptr, nbytes)
@@ -498,8 +510,13 @@ async def execute_read_reqs(
             finally:
                 pbuf.release()
                 alloc.notify()
+        finally:
+            if slot_held:
+                io_slots.release()
         bytes_read += nbytes
         rstats.device_bytes += nbytes
+        if _TRACE_READS:
+            rstats.trace.append((t_q - begin, t_s - begin, t_p - begin, t_r - begin, time.monotonic() - begin, nbytes))
 
     budget = memory_budget_bytes
     budget_freed = asyncio.Event()
