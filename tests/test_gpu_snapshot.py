@@ -21,6 +21,10 @@ from torchsnapshot_b200.snapshot import Snapshot, StateDict
 pytestmark = pytest.mark.gpu
 
 
+def _ranged(buf, byte_range):
+    return buf if byte_range is None else buf[byte_range[0] : byte_range[1]]
+
+
 def sha(b) -> str:
     return hashlib.sha256(bytes(b)).hexdigest()
 
@@ -140,7 +144,7 @@ def test_gpu_reshard_all_layout_pairs(golden_dir, monkeypatch):
         rrs, _ = iop.ShardedTensorIOPreparer.prepare_read(entry, dst)
         for rr in rrs:
             assert rr.buffer_consumer.is_device_consumable()
-            run(rr.buffer_consumer.consume_buffer(staged[rr.path]))
+            run(rr.buffer_consumer.consume_buffer(_ranged(staged[rr.path], rr.byte_range)))
         assert [sha(_bytes(s.tensor)) for s in dst.local_shards()] == g["dst_sha256"], key
 
 

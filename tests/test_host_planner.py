@@ -33,6 +33,10 @@ from torchsnapshot_b200.manifest import Shard, ShardedTensorEntry, TensorEntry
 from torchsnapshot_b200.partitioner import assign_write_loads
 
 
+def _ranged(buf, byte_range):
+    return buf if byte_range is None else buf[byte_range[0] : byte_range[1]]
+
+
 def sha(b) -> str:
     return hashlib.sha256(bytes(b)).hexdigest()
 
@@ -108,7 +112,7 @@ def test_chunking_matches_reference(golden_dir):
         rrs, _ = ChunkedTensorIOPreparer.prepare_read(entry, out)
         staged = {wr.path: bytes(run(wr.buffer_stager.stage_buffer())) for wr in wrs}
         for rr in rrs:
-            run(rr.buffer_consumer.consume_buffer(staged[rr.path]))
+            run(rr.buffer_consumer.consume_buffer(_ranged(staged[rr.path], rr.byte_range)))
         assert oracle.serialize(out) == oracle.serialize(t)
 
 
@@ -180,13 +184,13 @@ def test_sharded_write_and_reshard_match_reference(golden_dir, monkeypatch):
                              for r in rr.buffer_consumer.overlapping_regions]} for rr in rrs]
         assert plan == g["plan"], key
         for rr in rrs:
-            run(rr.buffer_consumer.consume_buffer(stageds[src_name][rr.path]))
+            run(rr.buffer_consumer.consume_buffer(_ranged(stageds[src_name][rr.path], rr.byte_range)))
         assert [sha(oracle.serialize(s.tensor)) for s in dst.local_shards()] == g["dst_sha256"], key
     # sharded -> dense tensor (read_object of a sharded entry)
     dense = torch.zeros(shape, dtype=full.dtype)
     rrs, _ = ShardedTensorIOPreparer.prepare_read(entries["dim1x3"], dense)
     for rr in rrs:
-        run(rr.buffer_consumer.consume_buffer(stageds["dim1x3"][rr.path]))
+        run(rr.buffer_consumer.consume_buffer(_ranged(stageds["dim1x3"][rr.path], rr.byte_range)))
     assert sha(oracle.serialize(dense)) == gold["dense_sha256"]
 
 
@@ -273,3 +277,51 @@ def test_speed_weighted_partition_balances_finish_time():
     assert max(finish) < 10 * 100 / 26.5  # better than the byte-balanced plan on these links
     # unusable speed vectors fall back to byte balance
     assert assign_write_loads(loads, [0, 0, 0, 0], [1.0, None, 1.0, 1.0]) == even
+
+
+def test_merged_reads_split_at_large_holes():
+    mk = lambda lo, hi: ReadReq(path="slab", byte_range=(lo, hi), buffer_consumer=prepare_read(
+        TensorEntry("slab", "buffer_protocol", "torch.uint8", [hi - lo], False, [lo, hi]), torch.zeros(hi - lo, dtype=torch.uint8))[0][0].buffer_consumer)
+    rrs = [mk(0, 100), mk(100, 300), mk(64 << 20, (64 << 20) + 50), mk(300, 1000)]
+    merged = sorted(batch_read_requests(rrs), key=lambda r: r.byte_range)
+    assert [r.byte_range for r in merged] == [(0, 1000), (64 << 20, (64 << 20) + 50)]
+    assert sorted(merged[0].buffer_consumer.byte_range_to_buffer_consumer) == [(0, 100), (100, 300), (300, 1000)]
+
+
+def test_sharded_read_fetches_only_the_needed_rows():
+    """A destination that needs a few rows of a big persisted piece reads just those rows,
+    and loads the same values as a whole-piece read."""
+    full = _cases.raw_tensor(9, [1000, 16], torch.float32)
+    entry, wrs = TensorIOPreparer.prepare_write("sharded/t_0_0", full)
+    sharded = ShardedTensorEntry(shards=[Shard(offsets=[0, 0], sizes=[1000, 16], tensor=entry)])
+    staged = bytes(run(wrs[0].buffer_stager.stage_buffer()))
+    # a plain tensor that covers rows 0..40 of the global tensor ("only the overlapping part is loaded")
+    out = torch.zeros(40, 16)
+    rrs, _ = ShardedTensorIOPreparer.prepare_read(sharded, out)
+    assert len(rrs) == 1 and rrs[0].byte_range == (0, 40 * 64)
+    run(rrs[0].buffer_consumer.consume_buffer(staged[rrs[0].byte_range[0] : rrs[0].byte_range[1]]))
+    assert torch.equal(out, full[:40])
+    # a local shard in the middle: rows 300..420 of the piece, columns 4..12
+    class Mid:
+        def __init__(self):
+            from types import SimpleNamespace as NS
+            self._s = [NS(tensor=torch.zeros(120, 8), metadata=NS(shard_offsets=[300, 4], shard_sizes=[120, 8]))]
+        def local_shards(self): return self._s
+        def metadata(self):
+            from types import SimpleNamespace as NS
+            return NS(size=[1000, 16])
+    import torchsnapshot_b200.io_preparer as iop
+    mid = Mid()
+    orig = iop._is_sharded_tensor
+    iop._is_sharded_tensor = lambda o: isinstance(o, Mid)
+    try:
+        rrs, _ = ShardedTensorIOPreparer.prepare_read(sharded, mid)
+    finally:
+        iop._is_sharded_tensor = orig
+    assert rrs[0].byte_range == (300 * 64, 420 * 64)
+    assert rrs[0].buffer_consumer.entry.shape == [120, 16]
+    run(rrs[0].buffer_consumer.consume_buffer(staged[rrs[0].byte_range[0] : rrs[0].byte_range[1]]))
+    assert torch.equal(mid._s[0].tensor, full[300:420, 4:12])
+    # a destination that needs (nearly) everything keeps the single whole-object read
+    rrs, _ = ShardedTensorIOPreparer.prepare_read(sharded, torch.zeros(990, 16))
+    assert rrs[0].byte_range is None

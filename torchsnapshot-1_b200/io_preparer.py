@@ -594,6 +594,46 @@ class ShardedTensorIOPreparer:
             return [(obj_out, [0] * obj_out.ndim, list(obj_out.shape))]
         raise RuntimeError(f"obj_out must either be a Tensor or ShardedTensor (got {type(obj_out)})")
 
+    @staticmethod
+    def _trim_piece_to_needed_rows(
+        piece: TensorEntry, regions: List["_OverlappingRegion"]
+    ) -> Tuple[TensorEntry, List["_OverlappingRegion"]]:
+        """Read only the rows of a persisted piece that some local shard overlaps.
+
+        The reference reads every overlapping piece whole -- up to 512 MiB for a sliver
+        (sharded_tensor.py:249-267).  Rows of a dense row-major piece are contiguous in storage, so the
+        needed rows [lo, hi) of dim 0 are one byte range; the piece entry is narrowed to it and the
+        source offsets of the overlap regions are shifted by lo.  Pickled (torch_save) pieces and
+        pieces that are needed (almost) whole are left alone."""
+        if piece.serializer != Serializer.BUFFER_PROTOCOL.value or not piece.shape or not regions:
+            return piece, regions
+        rows = piece.shape[0]
+        lo, hi = rows, 0
+        for r in regions:
+            _dim, src_off, _dst_off, length = r.overlap_region[0]
+            lo = min(lo, src_off)
+            hi = max(hi, src_off + length)
+        if lo >= hi or (hi - lo) * 8 > rows * 7:  # less than 1/8 to save: one whole-object read is simpler
+            return piece, regions
+        row_bytes = dtype_to_element_size(string_to_dtype(piece.dtype)) * reduce(mul, piece.shape[1:], 1)
+        base = 0 if piece.byte_range is None else piece.byte_range[0]
+        trimmed = TensorEntry(
+            location=piece.location,
+            serializer=piece.serializer,
+            dtype=piece.dtype,
+            shape=[hi - lo] + list(piece.shape[1:]),
+            replicated=piece.replicated,
+            byte_range=[base + lo * row_bytes, base + hi * row_bytes],
+        )
+        shifted = [
+            _OverlappingRegion(
+                dst_tensor=r.dst_tensor,
+                overlap_region=[(d, so - lo if d == 0 else so, do, ln) for d, so, do, ln in r.overlap_region],
+            )
+            for r in regions
+        ]
+        return trimmed, shifted
+
     @classmethod
     def prepare_read(
         cls, entry: ShardedTensorEntry, obj_out: Optional[Any] = None
@@ -621,13 +661,12 @@ class ShardedTensorIOPreparer:
             key = (shard.tensor.location, shard.tensor.byte_range_tuple)
             if key not in regions_by_piece:
                 continue
+            piece_entry, regions = cls._trim_piece_to_needed_rows(shard.tensor, regions_by_piece[key])
             read_reqs.append(
                 ReadReq(
-                    path=shard.tensor.location,
-                    buffer_consumer=ShardedTensorBufferConsumer(
-                        overlapping_regions=regions_by_piece[key], entry=shard.tensor
-                    ),
-                    byte_range=shard.tensor.byte_range_tuple,
+                    path=piece_entry.location,
+                    buffer_consumer=ShardedTensorBufferConsumer(overlapping_regions=regions, entry=piece_entry),
+                    byte_range=piece_entry.byte_range_tuple,
                 )
             )
         return read_reqs, Future(obj=obj_out)
