@@ -240,3 +240,37 @@ def test_non_batched_large_tensors_and_chunks(tmp_path):
         snap.restore({"st": out})
     for k in state:
         assert torch.equal(out[k], state[k]), k
+
+
+def test_read_object_row_block_from_sharded_table(tmp_path, monkeypatch):
+    """BASELINE config 4 style random access: read a block of rows of a row-wise sharded table into a
+    CUDA tensor.  Only the needed rows of the persisted pieces are read from storage."""
+    import torchsnapshot_b200.io_preparer as iop
+    import torchsnapshot_b200.snapshot as snapmod
+    from torchsnapshot_b200.storage_plugins.fs import FSStoragePlugin
+
+    rows, cols = 60000, 128
+    full = _cases.raw_tensor(321, [rows, cols], torch.float32)
+    monkeypatch.setattr(iop, "_is_sharded_tensor", lambda o: isinstance(o, _Fake))
+    monkeypatch.setattr(snapmod, "_is_sharded_tensor", lambda o: isinstance(o, _Fake))
+    monkeypatch.setattr(_Fake, "metadata", lambda self: type("M", (), {"size": self._shape})(), raising=False)
+    monkeypatch.setattr(_Fake, "sharding_spec", lambda self: None, raising=False)
+    table = _Fake(_cases.chunk_boxes([rows, cols], 0, 4), full.dtype, [rows, cols], "cuda", full)
+    with knobs.override_max_shard_size_bytes(4 << 20), knobs.override_slab_size_threshold_bytes(1 << 20):
+        snap = Snapshot.take(str(tmp_path / "s"), {"emb": StateDict(t=table)})
+    read_bytes = []
+
+    class Counting(FSStoragePlugin):
+        async def read_into(self, path, byte_range, out):
+            read_bytes.append(len(out))
+            await super().read_into(path, byte_range, out)
+
+    monkeypatch.setattr(snapmod, "url_to_storage_plugin", lambda path, opts=None: Counting(path))
+    out = torch.zeros(5000, cols, device="cuda")  # rows 0..5000 of the global table
+    got = snap.read_object("0/emb/t", obj_out=out)
+    assert got is out and _bytes(out) == oracle.serialize(full[:5000])
+    assert sum(read_bytes) == 5000 * cols * 4, (sum(read_bytes), len(read_bytes))  # not the 4 MiB pieces
+    # the whole table into a dense CUDA tensor
+    dense = torch.zeros(rows, cols, device="cuda")
+    snap.read_object("0/emb/t", obj_out=dense)
+    assert _bytes(dense) == oracle.serialize(full)
