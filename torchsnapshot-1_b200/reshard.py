@@ -313,7 +313,9 @@ def p2p_restore_units(
         async def read_all() -> None:
             loop = asyncio.get_running_loop()
             alloc = _Allocator()
-            sem = asyncio.Semaphore(32)
+            from .scheduler import io_concurrency
+
+            sem = asyncio.Semaphore(io_concurrency())
 
             async def one(key: UnitKey) -> None:
                 nbytes = sizes[key]

@@ -46,6 +46,22 @@ _MAX_PER_RANK_CPU_CONCURRENCY: int = int(os.environ.get("TSB200_CPU_CONCURRENCY"
 # storage operations in flight per rank.  The reference uses 16 (scheduler.py:30); 32 single-threaded
 # writers measured best on the B200 box (tmpfs: 28.8 vs 26.6 GB/s end-to-end take), TSB200_IO_CONCURRENCY overrides.
 _MAX_PER_RANK_IO_CONCURRENCY: int = int(os.environ.get("TSB200_IO_CONCURRENCY", "32"))
+_local_world_size: int = 1
+
+
+def set_local_world_size(n: int) -> None:
+    """Ranks sharing this host (Snapshot tells the scheduler): storage concurrency is per host, not per rank."""
+    global _local_world_size
+    _local_world_size = max(int(n), 1)
+
+
+def io_concurrency() -> int:
+    """Storage operations in flight for this rank: the knob if set, else 2 per host core available to this
+    rank, within [4, 32] (8 ranks on a 32-core host otherwise run 256 reader threads and thrash)."""
+    if "TSB200_IO_CONCURRENCY" in os.environ:
+        return _MAX_PER_RANK_IO_CONCURRENCY
+    cores = os.cpu_count() or 8
+    return max(4, min(_MAX_PER_RANK_IO_CONCURRENCY, 2 * cores // _local_world_size))
 _TRACE_READS = os.environ.get("TSB200_TRACE_READS") == "1"
 _STAGING_ALIGN = 512  # each file's bytes start 512-B aligned inside the device staging block
 
@@ -270,7 +286,7 @@ async def execute_write_reqs(
     stats = _Stats()
     last_write_stats = stats
     tasks: Set["asyncio.Future[Any]"] = set()
-    io_slots = asyncio.Semaphore(_MAX_PER_RANK_IO_CONCURRENCY)
+    io_slots = asyncio.Semaphore(io_concurrency())
     alloc = _Allocator()
 
     device_reqs: Dict[int, List[WriteReq]] = defaultdict(list)
@@ -449,7 +465,7 @@ async def execute_read_reqs(
 ) -> None:
     loop = asyncio.get_running_loop()
     executor = ThreadPoolExecutor(max_workers=_MAX_PER_RANK_CPU_CONCURRENCY, thread_name_prefix="tsb-consume")
-    io_slots = asyncio.Semaphore(_MAX_PER_RANK_IO_CONCURRENCY)
+    io_slots = asyncio.Semaphore(io_concurrency())
     alloc = _Allocator()
     global last_read_stats
     rstats = _ReadStats()

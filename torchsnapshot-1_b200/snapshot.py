@@ -50,6 +50,7 @@ from .scheduler import (
     PendingIOWork,
     _MAX_PER_RANK_MEMORY_BUDGET_BYTES,
     get_process_memory_budget_bytes,
+    set_local_world_size,
     sync_execute_read_reqs,
     sync_execute_write_reqs,
 )
@@ -212,6 +213,7 @@ class Snapshot:
         globs = set.intersection(*(set(h[1]) for h in hello))
         global_keys = sorted(set(itertools.chain.from_iterable(h[2] for h in hello)))
         local_world = sum(1 for h in hello if h[3] == hello[rank][3])
+        set_local_world_size(local_world)
         storage = url_to_storage_plugin(path, storage_options)
 
         # ---- state dicts -> flat leaves (RNG state first, restored afterwards) -----------------
@@ -314,6 +316,7 @@ class Snapshot:
         pg.all_gather_object(keys, (list(app_state.keys()), socket.gethostname()))
         global_keys = sorted(set(itertools.chain.from_iterable(k[0] for k in keys)))
         local_world = sum(1 for k in keys if k[1] == keys[rank][1])
+        set_local_world_size(local_world)
         budget = _memory_budget(local_world)
         rng_key = rng_items[0][0] if rng_items else None
         # keys every rank restores: only those can use the collective peer-to-peer reshard path
