@@ -127,3 +127,44 @@ def async_commit(rank, world, tmp):
     snap.restore({"s": out})
     assert torch.equal(out["t"], torch.arange(1000, dtype=torch.float32) + rank)
     assert os.path.exists(os.path.join(tmp, "snap", ".snapshot_metadata"))
+
+
+def _flat_sharded(world, rank_boxes_only=False):
+    """FSDP-style flat parameter: a 1-D ShardedTensor chunked over the ranks (BASELINE config 3 layout)."""
+    from torch.distributed._shard import sharded_tensor
+    from torch.distributed._shard.sharding_spec import ChunkShardingSpec
+
+    spec = ChunkShardingSpec(dim=0, placements=[f"rank:{r}/cpu" for r in range(world)])
+    return sharded_tensor.empty(spec, 10007, dtype=torch.float32)
+
+
+def elastic_take(rank, world, tmp):
+    import _cases
+    from torchsnapshot_b200 import knobs
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    full = _cases.raw_tensor(900, [10007], torch.float32)
+    st = _flat_sharded(world)
+    for shard in st.local_shards():
+        o, n = shard.metadata.shard_offsets[0], shard.metadata.shard_sizes[0]
+        shard.tensor.copy_(full[o : o + n])
+    rep = StateDict(w=_cases.raw_tensor(901, [33, 7], torch.float32), step=5)
+    with knobs.override_max_shard_size_bytes(4000):
+        Snapshot.take(os.path.join(tmp, "snap"), {"flat": StateDict(p=st), "rep": rep}, replicated=["rep/**"])
+
+
+def elastic_restore(rank, world, tmp):
+    """Restore at a different world size than the snapshot was taken with (8->4 / 4->8 in miniature)."""
+    import _cases
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    full = _cases.raw_tensor(900, [10007], torch.float32)
+    st = _flat_sharded(world)
+    rep = StateDict(w=torch.zeros(33, 7), step=0)
+    snap = Snapshot(os.path.join(tmp, "snap"))
+    assert snap.metadata.world_size == 2
+    snap.restore({"flat": StateDict(p=st), "rep": rep})
+    for shard in st.local_shards():
+        o, n = shard.metadata.shard_offsets[0], shard.metadata.shard_sizes[0]
+        assert torch.equal(shard.tensor, full[o : o + n]), (rank, o, n)
+    assert torch.equal(rep["w"], _cases.raw_tensor(901, [33, 7], torch.float32)) and rep["step"] == 5

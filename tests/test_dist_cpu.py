@@ -48,3 +48,12 @@ def test_sharded_take_and_reshard_restore(tmp_path):
 @pytest.mark.timeout(300)
 def test_async_take_commit_across_ranks(tmp_path):
     _launch("async_commit", tmp_path)
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("new_world", [1, 3])
+def test_elastic_restore_at_another_world_size(tmp_path, new_world):
+    """Taken by 2 ranks, restored by 1 and by 3: sharded entries are merged over the saving ranks and
+    re-cut for the loading ranks; replicated entries reach ranks that did not exist at save time."""
+    _launch("elastic_take", tmp_path, world=2)
+    _launch("elastic_restore", tmp_path, world=new_world)
