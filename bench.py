@@ -406,7 +406,7 @@ def main():
             "wall_ms_per_step": round(1e3 * sum(res["step_wall"]) / K, 1),
             "gpu_launches": int(total_launches),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                         "frac": round(achieved / peak, 4), "traffic": traffic, "kernel": "tsb_copy_flat_kernel",
+                         "frac": round(achieved / peak, 4), "traffic": traffic, "kernel": "tsb_copy_flat_tma_kernel",
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": int(res["kern_bytes"][0]) if res["kern_bytes"] else 0,
                          "kernel_ms_per_launch": round(kern_total_ms / max(K, 1), 4)},

@@ -7,6 +7,7 @@ from torchsnapshot_b200 import _native
 from torchsnapshot_b200.engine import get_engine
 from torchsnapshot_b200.regions import regions_to_array
 
+print('TSB200_USE_TMA =', os.environ.get('TSB200_USE_TMA'), flush=True)
 eng = get_engine(0); ctx = eng.ctx
 def timeit(arr, nbytes, iters=10, label=""):
     for _ in range(3): eng.copy_region_array(arr)

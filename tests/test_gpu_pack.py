@@ -257,3 +257,46 @@ def test_full_size_round_trip_c3(engine):
     mask[total:] = False
     assert torch.equal(out[mask], pool[mask])
     assert int(out[~mask].sum()) == 0
+
+
+@pytest.mark.parametrize("use_tma", ["1", "0"])
+def test_tma_and_lsu_variants_of_the_flat_kernel(golden_dir, monkeypatch, use_tma):
+    """Default: tiles aligned on both sides go through cp.async.bulk (TMA), everything else through the LSU
+    path of the same kernel.  TSB200_USE_TMA=0: the pure LSU kernel.  Both must give the oracle's bytes in
+    every alignment case."""
+    from torchsnapshot_b200 import engine as engmod
+
+    engmod.shutdown_engines()
+    monkeypatch.setenv("TSB200_USE_TMA", use_tma)
+    try:
+        eng = engmod.get_engine(0)
+        rs = np.random.RandomState(8)
+        src_h = rs.randint(0, 256, size=(6 << 20) + 64).astype(np.uint8)
+        src = torch.from_numpy(src_h).cuda()
+        jobs = []
+        d_off = 0
+        for n in (16, 4096, 32768, 32768 + 16, 1 << 20, (1 << 20) + 5, 100000):
+            for sa, da in ((0, 0), (0, 16), (16, 0), (0, 4), (4, 0), (1, 1), (3, 8)):
+                jobs.append((64 + sa, d_off + 32 + da, n))
+                d_off += n + 96
+        dst = torch.full((d_off + 64,), 0xEE, dtype=torch.uint8, device="cuda")
+        _launch(eng, [(src.data_ptr() + s, dst.data_ptr() + d, n, (), (), ()) for s, d, n in jobs])
+        want = np.full(d_off + 64, 0xEE, dtype=np.uint8)
+        for s, d, n in jobs:
+            want[d : d + n] = src_h[s : s + n]
+        assert np.array_equal(dst.cpu().numpy(), want)
+        # and the reference-made slab fixture
+        gold = json.load(open(os.path.join(golden_dir, "slab_mixed.json")))
+        threshold, items = _cases.slab_case_mixed()
+        cpu = {p: _cases.build_view(spec) for p, spec in items}
+        gpu = {p: _cases.build_view(spec, "cuda") for p, spec in items}
+        slabs, _ = planner.plan_slabs([(p, t.numel() * t.element_size(), True, True) for p, t in cpu.items()], threshold)
+        members = slabs[0][1]
+        slab = torch.zeros(members[-1][2], dtype=torch.uint8, device="cuda")
+        regions = []
+        for p, lo, _hi in members:
+            regions += pack_regions(gpu[p], slab.data_ptr() + lo)
+        _launch(eng, regions)
+        assert sha(_to_host(slab)) == gold["slabs"][0]["sha256"]
+    finally:
+        engmod.shutdown_engines()

@@ -138,14 +138,50 @@ __device__ __forceinline__ void flat_shifted(uint4* __restrict__ d4, const uint4
   }
 }
 
-__global__ void __launch_bounds__(TSB_FLAT_THREADS)
-tsb_copy_flat_kernel(const TsbTile* __restrict__ tiles) {
+// ---- TMA (bulk async copy) helpers: global -> shared -> global without register staging ----------
+__device__ __forceinline__ uint32_t tsb_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// One tile whose source, destination and length are all multiples of 16 bytes: a single thread moves
+// it with cp.async.bulk (SASS: UBLKCP) through the CTA's shared-memory buffer.
+__device__ __forceinline__ void flat_tile_tma(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint32_t len,
+                                              uint8_t* smem, uint64_t* bar) {
+  const uint32_t bar_a = tsb_smem_u32(bar), buf_a = tsb_smem_u32(smem);
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(len) : "memory");
+  asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(buf_a),
+               "l"(src), "r"(len), "r"(bar_a)
+               : "memory");
+  asm volatile(
+      "{\n.reg .pred p;\nTSB_WAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n@p bra TSB_DONE_%=;\nbra "
+      "TSB_WAIT_%=;\nTSB_DONE_%=:\n}" ::"r"(bar_a)
+      : "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(buf_a), "r"(len) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+// USE_TMA = false: the pure LSU kernel (no shared memory, 32 registers, 2048 threads per SM).
+// USE_TMA = true : tiles that are 16-byte aligned on both sides go through cp.async.bulk; the rest (first
+//                  / last tile of a run, shifted sources) take the LSU path of the same kernel.  Launched
+//                  with TSB_TILE_BYTES of dynamic shared memory.  On B200 it is 0.8-1.7 % faster than the
+//                  LSU path on aligned tiles and identical elsewhere (profiles/r01_kernel_bench_tma.txt),
+//                  so it is the default; TSB200_USE_TMA=0 selects the LSU kernel.
+template <bool USE_TMA>
+__device__ __forceinline__ void flat_tile(const TsbTile* __restrict__ tiles, uint8_t* smem, uint64_t* bar) {
   const uint32_t tid = threadIdx.x;
   const uint4* tp = reinterpret_cast<const uint4*>(tiles + blockIdx.x);
   const uint4 t0 = __ldg(tp);
   const uint32_t len = __ldg(reinterpret_cast<const uint32_t*>(tp + 1));
   const uint8_t* src = reinterpret_cast<const uint8_t*>(((uint64_t)t0.y << 32) | t0.x);
   uint8_t* dst = reinterpret_cast<uint8_t*>(((uint64_t)t0.w << 32) | t0.z);
+  if (USE_TMA) {
+    if ((((uint32_t)(uintptr_t)src | (uint32_t)(uintptr_t)dst | len) & 15u) == 0 && len != 0) {
+      if (tid == 0) flat_tile_tma(dst, src, len, smem, bar);
+      return;
+    }
+  }
   // the host puts interior tile boundaries on 16-byte boundaries of the destination, so only the
   // first tile of a region has a head and only the last one a tail
   uint32_t head = (16u - ((uint32_t)(uintptr_t)dst & 15u)) & 15u;
@@ -185,6 +221,18 @@ tsb_copy_flat_kernel(const TsbTile* __restrict__ tiles) {
       default: flat_shifted<3>(d4, a4, nvec, sb, tid); break;
     }
   }
+}
+
+__global__ void __launch_bounds__(TSB_FLAT_THREADS)
+tsb_copy_flat_kernel(const TsbTile* __restrict__ tiles) {
+  flat_tile<false>(tiles, nullptr, nullptr);
+}
+
+__global__ void __launch_bounds__(TSB_FLAT_THREADS)
+tsb_copy_flat_tma_kernel(const TsbTile* __restrict__ tiles) {
+  extern __shared__ __align__(128) uint8_t tsb_tma_smem[];
+  __shared__ uint64_t tsb_tma_bar;
+  flat_tile<true>(tiles, tsb_tma_smem, &tsb_tma_bar);
 }
 
 // ---------------------------------------------------------------------------------------------

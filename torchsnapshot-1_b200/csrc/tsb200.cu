@@ -5,6 +5,7 @@
 #include <fcntl.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -224,6 +225,7 @@ struct TsbCtx {
   std::vector<uint32_t> free_events;
   std::vector<PendingScratch> pending;
   std::vector<cudaEvent_t> spare_scratch_events;
+  bool use_tma = true;  // aligned tiles through cp.async.bulk; TSB200_USE_TMA=0 turns it off
   // counters (tsb_ctx_counters)
   uint64_t n_kernel_launches = 0;  // expand + flat + strided kernels
   uint64_t n_copy_calls = 0;       // tsb_copy_regions calls that launched something
@@ -410,6 +412,18 @@ int tsb_ctx_create(int device, uint64_t host_arena_max, uint64_t dev_arena_max, 
     if (e != cudaSuccess) {
       delete ctx;
       return set_err(TSB_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e));
+    }
+  }
+  {
+    // default on: measured 0.8-1.7 % faster than the LSU path on aligned tiles and equal elsewhere
+    // (profiles/r01_kernel_bench_tma.txt); TSB200_USE_TMA=0 selects the pure LSU kernel
+    const char* tma = getenv("TSB200_USE_TMA");
+    ctx->use_tma = !(tma && tma[0] == '0');
+    if (ctx->use_tma &&
+        cudaFuncSetAttribute(tsb_copy_flat_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TSB_TILE_BYTES) !=
+            cudaSuccess) {
+      (void)cudaGetLastError();
+      ctx->use_tma = false;
     }
   }
   if (host_arena_max == 0) host_arena_max = 4ull << 30;
@@ -663,7 +677,10 @@ static int copy_regions_impl(TsbCtx* ctx, int stream, const TsbRegion* regions, 
     if (kernel_start) {
       if (event_lookup(ctx, *kernel_start, &ev_start) == TSB_OK) cudaEventRecord(ev_start, s);
     }
-    tsb_copy_flat_kernel<<<nt, TSB_FLAT_THREADS, 0, s>>>(tiles);
+    if (ctx->use_tma)
+      tsb_copy_flat_tma_kernel<<<nt, TSB_FLAT_THREADS, TSB_TILE_BYTES, s>>>(tiles);
+    else
+      tsb_copy_flat_kernel<<<nt, TSB_FLAT_THREADS, 0, s>>>(tiles);
     e = cudaGetLastError();
   } else if (kernel_start && event_lookup(ctx, *kernel_start, &ev_start) == TSB_OK) {
     cudaEventRecord(ev_start, s);
