@@ -337,7 +337,7 @@ def p2p_restore_units(
                             ctx.event_release(ev)
                     finally:
                         pbuf.release()
-                        alloc.notify()
+                        alloc.notify(nbytes)
                 finally:
                     if held:
                         sem.release()

@@ -184,24 +184,34 @@ async def _wait_event(loop: asyncio.AbstractEventLoop, executor: Optional[Execut
 
 
 class _Allocator:
-    """Arena allocation that waits (asynchronously) for a release instead of failing."""
+    """Arena allocation that waits (asynchronously) for a release instead of failing, and keeps the pinned
+    bytes in flight under the per-rank memory budget (the reference budgets its host staging buffers the
+    same way, scheduler.py:255-329: a request larger than the budget is admitted only when nothing else is
+    in flight)."""
 
-    def __init__(self) -> None:
+    def __init__(self, budget_bytes: Optional[int] = None) -> None:
         self.released = asyncio.Event()
         self.outstanding = 0  # allocations handed out through this object and not yet released
+        self.budget = budget_bytes
+        self.pinned_inflight = 0
 
-    def notify(self) -> None:
+    def notify(self, pinned_bytes: int = 0) -> None:
         self.outstanding -= 1
+        self.pinned_inflight -= pinned_bytes
         self.released.set()
 
     async def pinned(self, eng: Engine, nbytes: int) -> PinnedBuffer:
         while True:
-            try:
-                buf = eng.pinned(nbytes)
-                self.outstanding += 1
-                return buf
-            except ArenaFull:
-                await self._wait(eng, "pinned host")
+            over = self.budget is not None and self.pinned_inflight > 0 and self.pinned_inflight + nbytes > self.budget
+            if not over:
+                try:
+                    buf = eng.pinned(nbytes)
+                    self.outstanding += 1
+                    self.pinned_inflight += nbytes
+                    return buf
+                except ArenaFull:
+                    pass
+            await self._wait(eng, "pinned host")
 
     async def device(self, eng: Engine, nbytes: int) -> int:
         while True:
@@ -287,7 +297,7 @@ async def execute_write_reqs(
     last_write_stats = stats
     tasks: Set["asyncio.Future[Any]"] = set()
     io_slots = asyncio.Semaphore(io_concurrency())
-    alloc = _Allocator()
+    alloc = _Allocator(memory_budget_bytes)
 
     device_reqs: Dict[int, List[WriteReq]] = defaultdict(list)
     host_reqs: List[WriteReq] = []
@@ -323,8 +333,9 @@ async def execute_write_reqs(
         finally:
             eng.ctx.event_release(ev)
         view = pbuf.view()
+        nbytes = pbuf.nbytes
         del pbuf
-        await write_out(path, view, alloc.notify)
+        await write_out(path, view, lambda: alloc.notify(nbytes))
 
     async def drain_wave(eng: Engine, base: int, files: List[Tuple[str, int, int]], ev_pack: int) -> None:
         """D2H of every file of a packed wave, then release of the wave's staging block."""
@@ -466,7 +477,7 @@ async def execute_read_reqs(
     loop = asyncio.get_running_loop()
     executor = ThreadPoolExecutor(max_workers=_MAX_PER_RANK_CPU_CONCURRENCY, thread_name_prefix="tsb-consume")
     io_slots = asyncio.Semaphore(io_concurrency())
-    alloc = _Allocator()
+    alloc = _Allocator(memory_budget_bytes)
     global last_read_stats
     rstats = _ReadStats()
     last_read_stats = rstats
@@ -525,7 +536,7 @@ async def execute_read_reqs(
                     alloc.notify()
             finally:
                 pbuf.release()
-                alloc.notify()
+                alloc.notify(nbytes)
         finally:
             if slot_held:
                 io_slots.release()
