@@ -266,6 +266,10 @@ def main():
     if world > 1:
         dist.broadcast_object_list(base, src=0)
     base = base[0]
+    import atexit
+
+    if rank == 0:
+        atexit.register(shutil.rmtree, base, ignore_errors=True)  # never leave gigabytes in tmpfs behind
 
     import asyncio
 

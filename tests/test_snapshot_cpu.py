@@ -205,3 +205,28 @@ def test_edge_cases_the_reference_cannot_stage(tmp_path):
     snap.restore({"st": out})
     assert torch.equal(out["bf_odd"], state["bf_odd"]) and out["bf_scalar"].item() == 1.5
     assert torch.equal(out["after"], state["after"]) and out["empty"].shape == (0, 3)
+
+
+def test_custom_tensor_prepare_func_and_pickled_dtypes(tmp_path):
+    """`_custom_tensor_prepare_func` (reference snapshot.py:175-179, tensor.py:55-71): the prepared tensor is
+    what gets written, tensors with a prepare func are never batched; complex tensors go through torch.save."""
+    calls = []
+
+    def halve(path, tensor, tracing):
+        calls.append((path, tracing))
+        return tensor.to(torch.float16) if tensor.dtype == torch.float32 else tensor
+
+    state = StateDict(w=torch.arange(8, dtype=torch.float32), z=torch.ones(3, dtype=torch.complex64), k=torch.arange(4))
+    snap = Snapshot.take(str(tmp_path / "s"), {"st": state}, _custom_tensor_prepare_func=halve)
+    m = snap.get_manifest()
+    assert m["0/st/w"].dtype == "torch.float16" and m["0/st/w"].location == "0/st/w" and m["0/st/w"].byte_range is None
+    assert m["0/st/z"].serializer == "torch_save" and m["0/st/k"].location == "0/st/k"
+    assert ("st/w", True) in calls and ("st/w", False) in calls
+    assert os.path.getsize(os.path.join(str(tmp_path / "s"), "0/st/w")) == 16
+    out = StateDict(w=torch.zeros(8, dtype=torch.float16), z=torch.zeros(3, dtype=torch.complex64), k=torch.zeros(4, dtype=torch.int64))
+    snap.restore({"st": out})
+    assert torch.equal(out["w"], torch.arange(8, dtype=torch.float16)) and torch.equal(out["z"], state["z"])
+    # dtype mismatch on load: the entry's dtype wins and a new tensor is returned through load_state_dict
+    out2 = StateDict(w=torch.zeros(8, dtype=torch.float32), z=torch.zeros(3, dtype=torch.complex64), k=torch.zeros(4, dtype=torch.int64))
+    snap.restore({"st": out2})
+    assert out2["w"].dtype == torch.float16

@@ -141,7 +141,7 @@ class TensorBufferStager(BufferStager):
         return self.tensor.numel() * self.tensor.element_size()
 
     def pack_regions(self, dst_addr: int) -> List[RegionTuple]:
-        return pack_regions(self.tensor.detach(), dst_addr)
+        return pack_regions(self.tensor, dst_addr)  # only addresses and strides are read
 
     # -- BufferStager -------------------------------------------------------------------------
     async def stage_buffer(self, executor: Optional[Executor] = None) -> BufferType:
@@ -199,7 +199,7 @@ class TensorBufferConsumer(BufferConsumer):
         return TensorIOPreparer.get_tensor_size_from_entry(self.entry)
 
     def unpack_regions(self, src_addr: int) -> List[RegionTuple]:
-        return unpack_regions(src_addr, self.tensor.detach())
+        return unpack_regions(src_addr, self.tensor)
 
     # -- BufferConsumer ---------------------------------------------------------------------
     @staticmethod
