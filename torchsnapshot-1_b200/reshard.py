@@ -346,10 +346,20 @@ def p2p_restore_units(
             # the copy regions are built while the reads are in flight
             await asyncio.gather(build_regions(), *(one(k) for k in owned))
 
-        event_loop.run_until_complete(read_all())
+        failure: Optional[str] = None
+        try:
+            event_loop.run_until_complete(read_all())
+        except Exception as e:  # noqa: BLE001 - reported to every rank below
+            failure = f"rank {rank}: {type(e).__name__}: {e}"
         t_bar = time.monotonic()
         stats.phase_ms["read"] = 1e3 * (t_bar - t_read)
-        pg.barrier()  # every owner's units are resident in its staging block
+        # "every owner's units are resident" -- or somebody failed, and then everybody raises instead of
+        # waiting forever for bytes that will never arrive
+        verdicts: List[Any] = [None] * world
+        pg.all_gather_object(verdicts, failure)
+        failed = [v for v in verdicts if v is not None]
+        if failed:
+            raise RuntimeError("peer-to-peer restore failed while reading from storage: " + "; ".join(failed))
         t_copy = time.monotonic()
         stats.phase_ms["exchange"] = 1e3 * (t_copy - t_bar)
         # ---- ONE launch: own staging + peers' staging (over NVLink) -> this rank's tensors ---------------
