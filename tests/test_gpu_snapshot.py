@@ -311,3 +311,22 @@ def test_memory_budget_bounds_pinned_bytes_in_flight(tmp_path, monkeypatch):
     assert 0 < peak[0] <= budget + slab, peak[0]
     for k in state:
         assert torch.equal(out[k], state[k]), k
+
+
+def test_batching_disabled_on_gpu(golden_dir, tmp_path):
+    """TORCHSNAPSHOT_DISABLE_BATCHING: one file per tensor (reference knobs.py:52-55); the tensors still go
+    through one pack launch and the payload bytes are the reference's."""
+    gold = json.load(open(os.path.join(golden_dir, "slab_mixed.json")))
+    _threshold, items = _cases.slab_case_mixed()
+    state = StateDict({p: _cases.build_view(spec, "cuda") for p, spec in items})
+    with knobs.override_is_batching_disabled(True):
+        snap = Snapshot.take(str(tmp_path / "s"), {"st": state})
+        payloads, meta = _payloads(str(tmp_path / "s"))
+        for p, _spec in items:
+            e = meta["manifest"][f"0/st/{p}"]
+            assert e["location"] == f"0/st/{p}" and e["byte_range"] is None
+            assert payloads[f"0/st/{p}"] == gold["objects"][p]["sha256"], p
+        out = StateDict({p: torch.zeros_like(t) for p, t in state.items()})
+        snap.restore({"st": out})
+    for p in state:
+        assert _bytes(out[p]) == _bytes(state[p]), p
