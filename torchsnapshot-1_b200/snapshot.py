@@ -241,9 +241,15 @@ class Snapshot:
             rng_items[0][1].load_state_dict(rng_sd)
 
         # ---- plan --------------------------------------------------------------------------------
-        candidates = [
-            p for p, v in flattened.items() if not _is_sharded_tensor(v) and any(fnmatch.fnmatch(p, g) for g in globs)
-        ]
+        if "**" in globs:  # everything is replicated (benchmarks/ddp): no need to match 20 k paths one by one
+            candidates = [p for p, v in flattened.items() if not _is_sharded_tensor(v)]
+        elif globs:
+            candidates = [
+                p for p, v in flattened.items()
+                if not _is_sharded_tensor(v) and any(fnmatch.fnmatch(p, g) for g in globs)
+            ]
+        else:
+            candidates = []
         if world > 1:
             # ---- collective 2: which candidate paths exist on every rank ----------------------
             seen: List[Any] = [None] * world
