@@ -255,8 +255,7 @@ def p2p_restore_units(
     last_stats = stats  # only calls that had something to do are remembered
     eng = get_engine(device)
     ctx = eng.ctx
-    sizes = {}
-    locations = {}
+    sizes: Dict[UnitKey, int] = {}
     for d in gathered:
         for k, (_need, nbytes) in d.items():
             sizes[k] = max(sizes.get(k, 0), nbytes)
@@ -269,6 +268,7 @@ def p2p_restore_units(
         # ---- staging for the units this rank owns: ONE block when the arena allows it, so that every
         # peer maps a single IPC handle (cudaIpcOpenMemHandle costs milliseconds per handle) ----------
         total_owned = sum((sizes[k] + 511) // 512 * 512 for k in owned)
+        staging_error: Optional[str] = None
         if owned:
             try:
                 base = ctx.dev_alloc(total_owned)
@@ -278,13 +278,20 @@ def p2p_restore_units(
                     staged[k] = base + off
                     off += (sizes[k] + 511) // 512 * 512
             except Exception:  # larger than one arena segment can be: one block per unit
-                for k in owned:
-                    staged[k] = ctx.dev_alloc(sizes[k])
-                    blocks.append(staged[k])
+                staged.clear()
+                try:
+                    for k in owned:
+                        staged[k] = ctx.dev_alloc(sizes[k])
+                        blocks.append(staged[k])
+                except Exception as e:  # noqa: BLE001 - told to every rank right below
+                    staging_error = f"rank {rank}: no device staging for {total_owned} bytes ({e})"
         # ---- addresses are known before any byte is read: publish them now (IPC handle + offset) ---
-        exports = {k: ctx.ipc_export(dptr) for k, dptr in staged.items()}
+        exports: Any = staging_error or {k: ctx.ipc_export(dptr) for k, dptr in staged.items()}
         all_exports: List[Any] = [None] * world
         pg.all_gather_object(all_exports, exports)
+        errors = [x for x in all_exports if isinstance(x, str)]
+        if errors:  # every rank sees the same list, so every rank raises instead of waiting on a peer
+            raise RuntimeError("peer-to-peer restore could not stage its reads: " + "; ".join(errors))
         t_read = time.monotonic()
         stats.phase_ms["plan"] = 1e3 * (t_read - t_begin)
         regions: List[RegionTuple] = []
