@@ -124,3 +124,44 @@ def ddp_replicated(rank, world, tmp):
         del os.environ["TSB200_P2P_RESHARD"]
     m = snap.get_manifest()
     assert all(m[f"0/m/p{i}"].replicated for i in range(12)) and "1/m/p0" not in m
+
+
+def _flat_cuda(world, rank, n=200003):
+    from torch.distributed._shard import sharded_tensor
+    from torch.distributed._shard.sharding_spec import ChunkShardingSpec
+
+    spec = ChunkShardingSpec(dim=0, placements=[f"rank:{r}/cuda:{r}" for r in range(world)])
+    return sharded_tensor.empty(spec, n, dtype=torch.float32)
+
+
+def elastic_take(rank, world, tmp):
+    """FSDP-style flat parameter (BASELINE config 3 layout) + replicated state, saved by `world` ranks."""
+    import _cases
+    from torchsnapshot_b200 import knobs
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    full = _cases.raw_tensor(900, [200003], torch.float32)
+    st = _flat_cuda(world, rank)
+    for shard in st.local_shards():
+        o, n = shard.metadata.shard_offsets[0], shard.metadata.shard_sizes[0]
+        shard.tensor.copy_(full[o : o + n])
+    rep = StateDict(w=_cases.raw_tensor(901, [333, 7], torch.float32).cuda(), step=5)
+    with knobs.override_max_shard_size_bytes(100000):
+        Snapshot.take(os.path.join(tmp, "snap"), {"flat": StateDict(p=st), "rep": rep}, replicated=["rep/**"])
+
+
+def elastic_restore(rank, world, tmp):
+    """...restored by another number of ranks (8->4 / 4->8 in miniature), on the GPUs."""
+    import _cases
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    full = _cases.raw_tensor(900, [200003], torch.float32)
+    st = _flat_cuda(world, rank)
+    for shard in st.local_shards():
+        shard.tensor.zero_()
+    rep = StateDict(w=torch.zeros(333, 7, device="cuda"), step=0)
+    Snapshot(os.path.join(tmp, "snap")).restore({"flat": StateDict(p=st), "rep": rep})
+    for shard in st.local_shards():
+        o, n = shard.metadata.shard_offsets[0], shard.metadata.shard_sizes[0]
+        assert torch.equal(shard.tensor.cpu(), full[o : o + n]), (rank, o, n)
+    assert torch.equal(rep["w"].cpu(), _cases.raw_tensor(901, [333, 7], torch.float32)) and rep["step"] == 5

@@ -48,3 +48,12 @@ def test_p2p_reshard_restore_two_gpus(tmp_path):
 @pytest.mark.timeout(400)
 def test_replicated_take_restore_two_gpus(tmp_path):
     _launch("ddp_replicated", tmp_path)
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("save_world,load_world", [(2, 1), (1, 2)])
+def test_elastic_reshard_between_world_sizes(tmp_path, save_world, load_world):
+    """Saved by `save_world` GPUs, restored by `load_world`: the flat sharded parameter is re-cut (through
+    the peer-to-peer path when more than one rank loads), replicated state reaches new ranks."""
+    _launch("elastic_take", tmp_path, world=save_world)
+    _launch("elastic_restore", tmp_path, world=load_world)
