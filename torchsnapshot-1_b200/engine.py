@@ -66,7 +66,6 @@ class Engine:
         self.host_bound = host_bound
         self.dev_bound = dev_bound
         self.launches = 0  # pack/unpack kernel launches issued (bench.py's gpu_launches)
-        self.kernel_bytes = 0
 
     # -- launches -------------------------------------------------------------------------------
     def copy_regions(self, regions: Sequence[RegionTuple], stream: int = STREAM_PACK) -> None:

@@ -38,6 +38,7 @@ from .serialization import Serializer, dtype_to_element_size, string_to_dtype
 logger: logging.Logger = logging.getLogger(__name__)
 
 Box = Tuple[List[int], List[int]]  # (global offsets, sizes)
+UnitKey = Tuple[str, int, int]  # (storage location, lower byte, upper byte; -1,-1 = whole object)
 
 
 @dataclass
@@ -51,10 +52,6 @@ class Piece:
     sizes: List[int]
     dtype: str
     nbytes: int
-
-    @property
-    def key(self) -> Tuple[str, str, Optional[Tuple[int, int]]]:
-        return (self.path, self.location, self.byte_range)
 
 
 def pieces_of(path: str, entry: ShardedTensorEntry) -> List[Piece]:
@@ -79,26 +76,24 @@ def _overlap_bytes(piece: Piece, box: Box, elsize: int) -> int:
 
 
 def plan_owners(pieces: Sequence[Piece], boxes_by_rank: Sequence[Dict[str, List[Box]]]) -> List[Optional[int]]:
-    """Owner rank of every piece (None if nobody needs it).  Deterministic: every rank computes the same
-    answer from the same inputs.  The owner is a rank with the largest overlap with the piece (so that as
-    few bytes as possible cross NVLink); among (near-)equal candidates the one that has been given the
-    fewest bytes so far (so that storage reads are spread over the ranks)."""
-    load = [0] * len(boxes_by_rank)
-    owners: List[Optional[int]] = []
-    for piece in pieces:
-        elsize = dtype_to_element_size(string_to_dtype(piece.dtype))
-        need = [
-            sum(_overlap_bytes(piece, box, elsize) for box in boxes.get(piece.path, [])) for boxes in boxes_by_rank
-        ]
-        best = max(need)
-        if best == 0:
-            owners.append(None)
-            continue
-        candidates = [r for r, n in enumerate(need) if n * 1000 >= best * 999]
-        owner = min(candidates, key=lambda r: (load[r], r))
-        load[owner] += piece.nbytes
-        owners.append(owner)
-    return owners
+    """Owner rank of every piece (None if nobody needs it), from every rank's local boxes.  Deterministic:
+    every rank computes the same answer from the same inputs.  The owner is a rank with the largest
+    overlap with the piece (so that as few bytes as possible cross NVLink); among (near-)equal candidates
+    the one that has been given the fewest bytes so far (so that storage reads are spread over the ranks).
+    Same rule, same code as the runtime plan (`plan_unit_owners`)."""
+    needs: List[Dict[UnitKey, Tuple[int, int]]] = []
+    keys = [(p.location, p.byte_range[0], p.byte_range[1]) if p.byte_range is not None else (p.location, -1, -1)
+            for p in pieces]
+    for boxes in boxes_by_rank:
+        mine: Dict[UnitKey, Tuple[int, int]] = {}
+        for piece, key in zip(pieces, keys):
+            elsize = dtype_to_element_size(string_to_dtype(piece.dtype))
+            need = sum(_overlap_bytes(piece, box, elsize) for box in boxes.get(piece.path, []))
+            if need:
+                mine[key] = (need, piece.nbytes)
+        needs.append(mine)
+    owners = plan_unit_owners(needs)
+    return [owners.get(key) for key in keys]
 
 
 def cross_rank_bytes(pieces: Sequence[Piece], owners: Sequence[Optional[int]],
@@ -143,9 +138,6 @@ class ReshardStats:
 
 
 last_stats: Optional[ReshardStats] = None
-
-UnitKey = Tuple[str, int, int]  # (storage location, lower byte, upper byte; -1,-1 = whole object)
-
 
 @dataclass
 class Unit:
