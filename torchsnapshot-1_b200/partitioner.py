@@ -163,11 +163,10 @@ def consolidate_replicated_entries(rank_to_entries: List[Dict[str, Entry]], dedu
         )
     replicated: Dict[str, Entry] = {}
     for entries in rank_to_entries:
-        for path in list(entries.keys()):
-            entry = entries[path]
-            if not is_replicated(entry):
-                continue
-            replicated.setdefault(path, merged_chunked.get(path, entry))
+        mine = [path for path, entry in entries.items() if getattr(entry, "replicated", False)]
+        for path in mine:
+            if path not in replicated:
+                replicated[path] = merged_chunked.get(path, entries[path])
             del entries[path]
     for rank, entries in enumerate(rank_to_entries):
         if dedup and rank != 0:

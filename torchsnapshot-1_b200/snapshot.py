@@ -291,11 +291,13 @@ class Snapshot:
         # ---- collective 3: the manifest ----------------------------------------------------------
         manifests: List[Any] = [None] * world
         pg.all_gather_object(manifests, manifest)
-        manifests = consolidate_replicated_entries(manifests)
+        if world > 1:  # with one rank every replicated entry already sits under rank 0
+            manifests = consolidate_replicated_entries(manifests)
         global_manifest: Manifest = {}
         for r, m in enumerate(manifests):
+            prefix = f"{r}/"
             for logical_path, entry in m.items():
-                global_manifest[os.path.join(str(r), logical_path)] = entry
+                global_manifest[prefix + logical_path] = entry
 
         pending = sync_execute_write_reqs(
             write_reqs=write_reqs,
