@@ -330,3 +330,30 @@ def test_batching_disabled_on_gpu(golden_dir, tmp_path):
         snap.restore({"st": out})
     for p in state:
         assert _bytes(out[p]) == _bytes(state[p]), p
+
+
+def test_overlapping_async_and_sync_takes(tmp_path):
+    """An async take still draining in its background thread while the next take starts: the arenas and
+    streams are process-wide and shared (SURVEY 8b threading); both snapshots must be complete and exact."""
+    g = torch.Generator(device="cuda").manual_seed(4)
+    a = StateDict({f"a{i}": torch.randn(1 << 20, device="cuda", generator=g) for i in range(24)})
+    b = StateDict({f"b{i}": torch.randn(1 << 19, device="cuda", generator=g) for i in range(24)})
+    want_a = {k: v.clone() for k, v in a.items()}
+    pending = Snapshot.async_take(str(tmp_path / "a"), {"s": a})
+    for v in a.values():
+        v.add_(1.0)
+    snap_b = Snapshot.take(str(tmp_path / "b"), {"s": b})
+    pending2 = Snapshot.async_take(str(tmp_path / "a2"), {"s": a})
+    snap_a = pending.wait()
+    snap_a2 = pending2.wait()
+    out_a = StateDict({k: torch.zeros_like(v) for k, v in a.items()})
+    snap_a.restore({"s": out_a})
+    for k in want_a:
+        assert torch.equal(out_a[k], want_a[k]), k
+    snap_a2.restore({"s": out_a})
+    for k in a:
+        assert torch.equal(out_a[k], a[k]), k
+    out_b = StateDict({k: torch.zeros_like(v) for k, v in b.items()})
+    snap_b.restore({"s": out_b})
+    for k in b:
+        assert torch.equal(out_b[k], b[k]), k
