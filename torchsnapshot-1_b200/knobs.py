@@ -53,6 +53,13 @@ def is_p2p_reshard_enabled() -> bool:
     return os.getenv("TSB200_P2P_RESHARD", "1").lower() not in ("0", "false")
 
 
+def trim_arenas_after_use() -> bool:
+    """TSB200_TRIM_ARENAS=1: give the device staging and pinned host segments back to the driver when a
+    take / restore has drained (a trainer short of HBM wants its memory back; the next take then pays for
+    cudaMalloc / cudaHostAlloc again).  Default: keep them for the next checkpoint."""
+    return os.getenv("TSB200_TRIM_ARENAS", "0").lower() in ("1", "true")
+
+
 def get_io_threads() -> int:
     return _int_env(_IO_THREADS_ENV_VAR, 0)
 

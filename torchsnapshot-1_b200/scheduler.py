@@ -32,7 +32,7 @@ from typing import Any, Dict, List, Optional, Set, Tuple
 
 import psutil
 
-from . import _native
+from . import _native, knobs
 from ._native import ArenaFull, STREAM_D2H, STREAM_H2D, STREAM_PACK
 from .engine import Engine, PinnedBuffer, get_engine, readonly_buffer_address
 from .regions import regions_to_array
@@ -263,6 +263,9 @@ class PendingIOWork:
         finally:
             self.executor.shutdown(wait=False)
         self.stats.writes_done = time.monotonic()
+        if knobs.trim_arenas_after_use():
+            for eng in {e for e, _a, _b, _n in self.stats.pack_events}:
+                eng.ctx.arena_trim()
         try:  # feed the replicated-write partitioner with this rank's measured device->host speed
             from .partitioner import record_take_speed
 
@@ -589,6 +592,11 @@ async def execute_read_reqs(
     finally:
         executor.shutdown(wait=False)
     rstats.bytes = bytes_read
+    if knobs.trim_arenas_after_use():
+        from .engine import _engines
+
+        for eng in list(_engines.values()):
+            eng.ctx.arena_trim()
     elapsed = max(time.monotonic() - begin, 1e-9)
     logger.info(f"Rank {rank} finished loading. Throughput: {bytes_read / 1024**2 / elapsed:.2f}MB/s")
 
