@@ -1,31 +1,51 @@
-"""The drop-in boundary types of the hot path.
+"""The drop-in boundary of the hot path, as Python types.
 
-Mirror of the reference's torchsnapshot/io_types.py:16-111 (same names, fields, argument
-meaning): BufferStager / BufferConsumer are what the schedulers drive, WriteReq / ReadReq what
-the planners emit, StoragePlugin the unchanged sink.  Any object with these methods works
-(duck typing), so reference stagers and third-party storage plugins interoperate.
+These are the reference's interface names with the reference's fields and call signatures
+(torchsnapshot/io_types.py:16-111), because everything on either side of the path is written against
+them: planners emit `WriteReq` / `ReadReq`, schedulers drive `BufferStager` / `BufferConsumer`, and the
+sink is any `StoragePlugin`.  Objects are matched structurally (duck typing) everywhere in this package,
+so stagers, consumers and plugins made by the reference interoperate without subclassing these.
 """
 
-import abc
 import asyncio
 import io
+from abc import ABC, abstractmethod
 from concurrent.futures import Executor
 from dataclasses import dataclass, field
-from typing import Generic, Optional, Tuple, TypeVar, Union
+from typing import Any, Awaitable, Generic, Optional, Tuple, TypeVar, Union
 
+# what a stager hands to the scheduler and the scheduler to StoragePlugin.write: immutable bytes, or a
+# memoryview (on this path: a view of a pinned arena block)
 BufferType = Union[bytes, memoryview]
+ByteRange = Tuple[int, int]
+T = TypeVar("T")
 
 
-class BufferStager(abc.ABC):
-    """Produces the bytes of one storage object (reference io_types.py:19-26)."""
+# ---- producers and consumers of one storage object ------------------------------------------------
+class BufferStager(ABC):
+    """Produces the bytes of one storage object.  `get_staging_cost_bytes` is what the scheduler charges
+    against the memory budget while the buffer is alive (reference io_types.py:19-26)."""
 
-    @abc.abstractmethod
-    async def stage_buffer(self, executor: Optional[Executor] = None) -> BufferType:
-        ...
-
-    @abc.abstractmethod
+    @abstractmethod
     def get_staging_cost_bytes(self) -> int:
-        ...
+        raise NotImplementedError
+
+    @abstractmethod
+    async def stage_buffer(self, executor: Optional[Executor] = None) -> BufferType:
+        raise NotImplementedError
+
+
+class BufferConsumer(ABC):
+    """Consumes the bytes of one storage object, or of the byte range its ReadReq names (reference
+    io_types.py:35-44)."""
+
+    @abstractmethod
+    def get_consuming_cost_bytes(self) -> int:
+        raise NotImplementedError
+
+    @abstractmethod
+    async def consume_buffer(self, buf: BufferType, executor: Optional[Executor] = None) -> None:
+        raise NotImplementedError
 
 
 @dataclass
@@ -34,33 +54,21 @@ class WriteReq:
     buffer_stager: BufferStager
 
 
-class BufferConsumer(abc.ABC):
-    """Consumes the bytes of one storage object or byte range (reference io_types.py:35-44)."""
-
-    @abc.abstractmethod
-    async def consume_buffer(self, buf: BufferType, executor: Optional[Executor] = None) -> None:
-        ...
-
-    @abc.abstractmethod
-    def get_consuming_cost_bytes(self) -> int:
-        ...
-
-
 @dataclass
 class ReadReq:
     path: str
     buffer_consumer: BufferConsumer
-    byte_range: Optional[Tuple[int, int]] = None
-
-
-T = TypeVar("T")
+    byte_range: Optional[ByteRange] = None  # None = the whole object
 
 
 @dataclass
 class Future(Generic[T]):
+    """Where a read deposits the object it produced (the reference's minimal future, io_types.py:57-59)."""
+
     obj: Optional[T] = None
 
 
+# ---- the storage sink --------------------------------------------------------------------------------
 @dataclass
 class WriteIO:
     path: str
@@ -71,33 +79,40 @@ class WriteIO:
 class ReadIO:
     path: str
     buf: io.BytesIO = field(default_factory=io.BytesIO)
-    byte_range: Optional[Tuple[int, int]] = None
+    byte_range: Optional[ByteRange] = None
 
 
-class StoragePlugin(abc.ABC):
-    """Unchanged storage sink ABI (reference io_types.py:75-111)."""
+def _run_sync(coro: Awaitable[Any], event_loop: Optional[asyncio.AbstractEventLoop]) -> None:
+    loop = event_loop if event_loop is not None else asyncio.new_event_loop()
+    loop.run_until_complete(coro)
 
-    @abc.abstractmethod
+
+class StoragePlugin(ABC):
+    """Unchanged sink ABI (reference io_types.py:75-111): four coroutines plus blocking conveniences.
+    A plugin may additionally offer `async read_into(path, byte_range, out: memoryview)`; the scheduler
+    then reads straight into pinned memory (see storage_plugins/fs.py)."""
+
+    @abstractmethod
     async def write(self, write_io: WriteIO) -> None:
-        ...
+        raise NotImplementedError
 
-    @abc.abstractmethod
+    @abstractmethod
     async def read(self, read_io: ReadIO) -> None:
-        ...
+        raise NotImplementedError
 
-    @abc.abstractmethod
+    @abstractmethod
     async def delete(self, path: str) -> None:
-        ...
+        raise NotImplementedError
 
-    @abc.abstractmethod
+    @abstractmethod
     async def close(self) -> None:
-        ...
+        raise NotImplementedError
 
     def sync_write(self, write_io: WriteIO, event_loop: Optional[asyncio.AbstractEventLoop] = None) -> None:
-        (event_loop or asyncio.new_event_loop()).run_until_complete(self.write(write_io=write_io))
+        _run_sync(self.write(write_io=write_io), event_loop)
 
     def sync_read(self, read_io: ReadIO, event_loop: Optional[asyncio.AbstractEventLoop] = None) -> None:
-        (event_loop or asyncio.new_event_loop()).run_until_complete(self.read(read_io=read_io))
+        _run_sync(self.read(read_io=read_io), event_loop)
 
     def sync_close(self, event_loop: Optional[asyncio.AbstractEventLoop] = None) -> None:
-        (event_loop or asyncio.new_event_loop()).run_until_complete(self.close())
+        _run_sync(self.close(), event_loop)
