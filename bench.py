@@ -318,10 +318,14 @@ def main():
             barrier()
             # (b) end-to-end take through the public API
             path = os.path.join(base, f"step{step}")
+            c_b0 = eng.ctx.counters()
             t0 = time.monotonic()
             snap = Snapshot.take(path, app_state, replicated=["**"])
             barrier()
             take_wall = time.monotonic() - t0
+            c_b1 = eng.ctx.counters()
+            take_desc_bytes = c_b1["desc_upload_bytes"] - c_b0["desc_upload_bytes"]  # host->device in take (b)
+            take_d2h_bytes = c_b1["kernel_payload_bytes"] - c_b0["kernel_payload_bytes"]  # packed, then copied out
             # (c) end-to-end restore
             reshard.last_stats = None
             t0 = time.monotonic()
@@ -388,8 +392,6 @@ def main():
     except Exception:
         pass
     launches = counters1["kernel_launches"] - counters0["kernel_launches"]
-    h2d_per_step = (counters1["desc_upload_bytes"] - counters0["desc_upload_bytes"]) / max(K, 1) + restore_h2d
-    my_take_bytes = res["kern_bytes"][0] // 2 if res["kern_bytes"] else 0
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -410,14 +412,15 @@ def main():
             "config": {"workload": WORKLOAD, "payload_bytes": P, "tensors": len(state),
                        "storage": f"FSStoragePlugin on {tmp_root()} (tmpfs)", "l2": "inputs (9.3 GB) >> 126 MB L2, no flush",
                        "partition": f"replicated writes partitioned over {world} rank(s)"},
-            "e2e": {"value": round(e2e_take, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step),
-                    "d2h_bytes_per_step": int(my_take_bytes * 3),
-                    "note": "Snapshot.take -> FSStoragePlugin, wall clock, max over ranks; per-rank bytes for takes (a)+(b)+(d)"},
+            "e2e": {"value": round(e2e_take, 3), "unit": UNIT, "h2d_bytes_per_step": int(take_desc_bytes),
+                    "d2h_bytes_per_step": int(take_d2h_bytes),
+                    "note": ("phase (b): Snapshot.take -> FSStoragePlugin, wall clock, max over ranks; bytes are this "
+                             "rank's: descriptor tables up, packed payload down (pinned host memory)")},
             "restore": {"value": round(e2e_restore, 3), "unit": UNIT,
                         "note": ("Snapshot.restore from tmpfs into CUDA tensors on every rank, wall clock; N > 1: each "
                                  "replicated byte is read from storage by one rank and fans out over NVLink"),
                         "unpack_kernel_ms": round(sum(res["unpack_ms"]) / K, 3),
-                        "nvlink_bytes_per_rank": int(restore_peer)},
+                        "h2d_bytes_per_step": int(restore_h2d), "nvlink_bytes_per_rank": int(restore_peer)},
             "async_take_blocked_ms": round(sum(res["blocked_ms"]) / K, 2),
             "wall_ms_per_step": round(1e3 * sum(res["step_wall"]) / K, 1),
             "gpu_launches": int(total_launches),
