@@ -230,3 +230,22 @@ def test_custom_tensor_prepare_func_and_pickled_dtypes(tmp_path):
     out2 = StateDict(w=torch.zeros(8, dtype=torch.float32), z=torch.zeros(3, dtype=torch.complex64), k=torch.zeros(4, dtype=torch.int64))
     snap.restore({"st": out2})
     assert out2["w"].dtype == torch.float16
+
+
+def test_pickled_dtypes_round_trip(tmp_path):
+    """Dtypes outside the buffer-protocol list (complex, quantized) are pickled with torch.save like in the
+    reference (tensor.py:68-71) and are never batched into slabs."""
+    q = torch.quantize_per_tensor(torch.randn(6, 5), scale=0.1, zero_point=3, dtype=torch.qint8)
+    state = StateDict(q=q, z=torch.randn(4, dtype=torch.complex128), f=torch.randn(3))
+    snap = Snapshot.take(str(tmp_path / "s"), {"st": state})
+    m = snap.get_manifest()
+    assert m["0/st/q"].serializer == "torch_save" and m["0/st/q"].dtype == "torch.qint8" and m["0/st/q"].byte_range is None
+    assert m["0/st/z"].serializer == "torch_save" and m["0/st/f"].location.startswith("batched/")
+    out = StateDict(q=torch.quantize_per_tensor(torch.zeros(6, 5), scale=0.1, zero_point=3, dtype=torch.qint8),
+                    z=torch.zeros(4, dtype=torch.complex128), f=torch.zeros(3))
+    snap.restore({"st": out})
+    assert torch.equal(out["q"].int_repr(), q.int_repr()) and torch.equal(out["z"], state["z"])
+    got = snap.read_object("0/st/z")
+    assert torch.equal(got, state["z"])
+    with pytest.raises(RuntimeError, match="quantized"):
+        snap.read_object("0/st/q")  # no runtime object to learn the quantization parameters from
