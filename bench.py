@@ -403,6 +403,25 @@ def main():
             "restore_value": round(r["restore_gbps"], 4), "host_cores": r["host_cores"],
         }
 
+    gpu_path_port = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # the reference's own GPU take path (per-tensor D2D copy_ into a ByteTensor slab, pageable .cpu() per
+        # slab, 16 writers), restated in oracle/ref_path.py: the like-for-like predecessor, whole state
+        from oracle import ref_path
+
+        times = []
+        for i in range(2):
+            root = tempfile.mkdtemp(prefix="tsb_refgpu_", dir=tmp_root())
+            try:
+                torch.cuda.synchronize()
+                t0 = time.monotonic()
+                ref_path.take_gpu(root, state)
+                times.append(time.monotonic() - t0)
+            finally:
+                shutil.rmtree(root, ignore_errors=True)
+        gpu_path_port = {"value": round(P / times[-1] / 1e9, 3), "unit": UNIT, "kind": "port",
+                         "sample": "whole state on the GPU, oracle/ref_path.py take_gpu, tmpfs, 1 warm-up + 1 timed"}
+
     total_launches = sum_over_ranks(launches)
     if rank == 0:
         line = {
@@ -433,6 +452,8 @@ def main():
         }
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
+        if gpu_path_port is not None:
+            line["reference_gpu_path_port"] = gpu_path_port
         print(json.dumps(line), flush=True)
         shutil.rmtree(base, ignore_errors=True)
     if world > 1:

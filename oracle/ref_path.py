@@ -135,3 +135,47 @@ def restore(root: str, outputs: Dict[str, torch.Tensor]) -> None:
         c.result()
     io_pool.shutdown()
     cpu_pool.shutdown()
+
+
+def take_gpu(root: str, tensors: Dict[str, torch.Tensor], threshold: int = 128 << 20) -> Dict[str, dict]:
+    """The reference's own GPU take path, restated with the torch calls it makes (baseline only; this is
+    what the CUDA kernels replace):
+      per GPU slab, on the event-loop thread: gpu_buf = torch.cuda.ByteTensor(slab)      batcher.py:144
+        one D2D copy_ per member tensor (after .contiguous())                            batcher.py:151-155
+        gpu_buf.cpu(): blocking D2H into pageable memory                                 batcher.py:156
+      tensors >= threshold: tensor.to("cpu") in the 4-thread pool                        tensor.py:247-254
+      <= 16 concurrent whole-file writes in worker threads                               scheduler.py:277-289
+    """
+    manifest: Dict[str, dict] = {}
+    plan_in = []
+    for path, t in tensors.items():
+        manifest[f"0/{path}"] = {
+            "type": "Tensor", "location": f"0/{path}", "serializer": "buffer_protocol", "dtype": str(t.dtype),
+            "shape": list(t.shape), "replicated": False, "byte_range": None,
+        }
+        plan_in.append((path, t.numel() * t.element_size(), True, True))
+    slabs, passthrough = planner.plan_slabs(plan_in, threshold)
+    io_pool = ThreadPoolExecutor(max_workers=IO_THREADS)
+    cpu_pool = ThreadPoolExecutor(max_workers=CPU_THREADS)
+    futures = []
+    big = {path: cpu_pool.submit(lambda t: t.detach().to("cpu"), tensors[path]) for path in passthrough}
+    for _kind, members in slabs:
+        location = os.path.join("batched", str(uuid.uuid4()))
+        gpu_buf = torch.empty(members[-1][2], dtype=torch.uint8, device=next(iter(tensors.values())).device)
+        for path, lo, hi in members:
+            t = tensors[path].detach().contiguous()
+            gpu_buf[lo:hi].copy_(t.reshape(-1).view(torch.uint8))
+            e = manifest[f"0/{path}"]
+            e["location"] = location
+            e["byte_range"] = [lo, hi]
+        host = gpu_buf.cpu()
+        futures.append(io_pool.submit(_write_file, root, location, memoryview(host.numpy())))
+    for path, fut in big.items():
+        futures.append(io_pool.submit(_write_file, root, f"0/{path}", _as_memoryview(fut.result())))
+    for f in futures:
+        f.result()
+    io_pool.shutdown()
+    cpu_pool.shutdown()
+    doc = json.dumps({"version": "0.1.0", "world_size": 1, "manifest": manifest}, sort_keys=False, indent=2)
+    _write_file(root, ".snapshot_metadata", doc.encode("utf-8"))
+    return manifest

@@ -401,3 +401,19 @@ def test_full_size_ddp_state_take_and_restore(tmp_path_factory):
             assert torch.equal(out[k].reshape(-1).view(torch.uint8), v.reshape(-1).view(torch.uint8)), k
     finally:
         shutil.rmtree(d, ignore_errors=True)
+
+
+def test_port_of_the_reference_gpu_path_writes_reference_bytes(golden_dir, tmp_path):
+    """oracle/ref_path.take_gpu (bench.py's `reference_gpu_path_port` baseline) restates the reference's GPU
+    stager with torch calls; its files must hold the reference's bytes too."""
+    from oracle import ref_path
+
+    gold = json.load(open(os.path.join(golden_dir, "slab_mixed.json")))
+    threshold, items = _cases.slab_case_mixed()
+    tensors = {p: _cases.build_view(spec, "cuda") for p, spec in items}
+    manifest = ref_path.take_gpu(str(tmp_path / "s"), tensors, threshold)
+    for p, _spec in items:
+        e = manifest[f"0/{p}"]
+        buf = open(os.path.join(str(tmp_path / "s"), e["location"]), "rb").read()
+        lo, hi = e["byte_range"]
+        assert e["byte_range"] == gold["objects"][p]["byte_range"] and sha(buf[lo:hi]) == gold["objects"][p]["sha256"], p
