@@ -325,3 +325,24 @@ def test_sharded_read_fetches_only_the_needed_rows():
     # a destination that needs (nearly) everything keeps the single whole-object read
     rrs, _ = ShardedTensorIOPreparer.prepare_read(sharded, torch.zeros(990, 16))
     assert rrs[0].byte_range is None
+
+
+def test_merged_reads_stay_within_one_storage_object_size(monkeypatch):
+    """Tiles of a budgeted read (read_object with memory_budget_bytes) must not be merged back into one read
+    of the whole tensor: a merged read is one pinned buffer."""
+    import torchsnapshot_b200.batcher as b
+
+    monkeypatch.setattr(b, "_MAX_MERGED_READ_BYTES", 1000)
+    t = torch.zeros(4096, dtype=torch.uint8)
+    entry = TensorEntry("big", "buffer_protocol", "torch.uint8", [4096], False, None)
+    rrs, _ = TensorIOPreparer.prepare_read(entry, t, buffer_size_limit_bytes=256)
+    assert len(rrs) == 16
+    merged = b.batch_read_requests(rrs)
+    assert all(r.byte_range[1] - r.byte_range[0] <= 1000 for r in merged) and len(merged) >= 5
+    covered = sorted(r.byte_range for r in merged)
+    assert covered[0][0] == 0 and covered[-1][1] == 4096
+    assert all(a[1] == c[0] for a, c in zip(covered, covered[1:]))
+    payload = bytes(range(256)) * 16
+    for r in merged:
+        run(r.buffer_consumer.consume_buffer(payload[r.byte_range[0] : r.byte_range[1]]))
+    assert bytes(t.numpy()) == payload
