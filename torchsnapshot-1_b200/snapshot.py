@@ -429,7 +429,8 @@ class Snapshot:
             return entry.get_value()
         read_reqs, fut = prepare_read(entry=entry, obj_out=obj_out, buffer_size_limit_bytes=memory_budget_bytes)
         if not knobs.is_batching_disabled():
-            read_reqs = batch_read_requests(read_reqs=read_reqs)
+            # merged reads never exceed the caller's budget, so the tiles stay tiles
+            read_reqs = batch_read_requests(read_reqs=read_reqs, max_merged_bytes=memory_budget_bytes)
         event_loop = asyncio.new_event_loop()
         storage = url_to_storage_plugin(self.path, self._storage_options)
         sync_execute_read_reqs(
