@@ -307,7 +307,7 @@ def test_memory_budget_bounds_pinned_bytes_in_flight(tmp_path, monkeypatch):
         out = StateDict({k: torch.zeros_like(v) for k, v in state.items()})
         snap.restore({"st": out})
     slab = 8 << 20
-    assert 0 < take_peak <= budget + slab, take_peak     # descriptor scratch rides in the same arena
+    assert 0 < take_peak <= budget + slab, take_peak
     assert 0 < peak[0] <= budget + slab, peak[0]
     for k in state:
         assert torch.equal(out[k], state[k]), k

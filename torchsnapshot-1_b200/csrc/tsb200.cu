@@ -219,6 +219,10 @@ struct TsbCtx {
   cudaStream_t streams[TSB_NUM_STREAMS] = {};
   Arena* host_arena = nullptr;
   Arena* dev_arena = nullptr;
+  // descriptor / tile-table scratch of the launches: separate arenas, so that payload buffers filling the
+  // pinned or staging arena to their bound can never starve a launch of its (small) tables
+  Arena* scratch_host = nullptr;
+  Arena* scratch_dev = nullptr;
   std::mutex mu;  // events + scratch list
   std::vector<cudaEvent_t> events;
   std::vector<uint32_t> event_gen;
@@ -281,8 +285,8 @@ static void reap_scratch(TsbCtx* ctx, bool wait_all) {
     }
   }
   for (auto& p : done) {
-    if (p.hbuf) ctx->host_arena->free(p.hbuf);
-    if (p.dbuf) ctx->dev_arena->free(p.dbuf);
+    if (p.hbuf) ctx->scratch_host->free(p.hbuf);
+    if (p.dbuf) ctx->scratch_dev->free(p.dbuf);
   }
 }
 
@@ -430,6 +434,8 @@ int tsb_ctx_create(int device, uint64_t host_arena_max, uint64_t dev_arena_max, 
   if (dev_arena_max == 0) dev_arena_max = 16ull << 30;
   ctx->host_arena = new Arena(true, host_arena_max, 256ull << 20, 4096);
   ctx->dev_arena = new Arena(false, dev_arena_max, 256ull << 20, 512);
+  ctx->scratch_host = new Arena(true, 1ull << 30, 4ull << 20, 4096);
+  ctx->scratch_dev = new Arena(false, 4ull << 30, 16ull << 20, 512);
   *out = ctx;
   return TSB_OK;
 }
@@ -443,8 +449,12 @@ int tsb_ctx_destroy(TsbCtx* ctx) {
   for (int i = 0; i < TSB_NUM_STREAMS; ++i) cudaStreamDestroy(ctx->streams[i]);
   ctx->host_arena->destroy();
   ctx->dev_arena->destroy();
+  ctx->scratch_host->destroy();
+  ctx->scratch_dev->destroy();
   delete ctx->host_arena;
   delete ctx->dev_arena;
+  delete ctx->scratch_host;
+  delete ctx->scratch_dev;
   delete ctx;
   (void)cudaGetLastError();
   return TSB_OK;
@@ -518,6 +528,8 @@ int tsb_arena_trim(TsbCtx* ctx) {
   reap_scratch(ctx, false);
   ctx->host_arena->trim();
   ctx->dev_arena->trim();
+  ctx->scratch_host->trim();
+  ctx->scratch_dev->trim();
   return TSB_OK;
 }
 
@@ -655,11 +667,19 @@ static int copy_regions_impl(TsbCtx* ctx, int stream, const TsbRegion* regions, 
   const uint64_t upload = run_bytes + str_bytes + reg_bytes;
   const uint64_t tile_bytes = plan.flat_tiles * sizeof(TsbTile);
   uint64_t hbuf = 0, dbuf = 0;
-  rc = ctx->host_arena->alloc(upload, &hbuf);
+  rc = ctx->scratch_host->alloc(upload, &hbuf);
+  if (rc == TSB_EAGAIN) {  // tables of earlier launches still pending: wait for them, then retry once
+    reap_scratch(ctx, true);
+    rc = ctx->scratch_host->alloc(upload, &hbuf);
+  }
   if (rc != TSB_OK) return rc;
-  rc = ctx->dev_arena->alloc(upload + tile_bytes, &dbuf);
+  rc = ctx->scratch_dev->alloc(upload + tile_bytes, &dbuf);
+  if (rc == TSB_EAGAIN) {
+    reap_scratch(ctx, true);
+    rc = ctx->scratch_dev->alloc(upload + tile_bytes, &dbuf);
+  }
   if (rc != TSB_OK) {
-    ctx->host_arena->free(hbuf);
+    ctx->scratch_host->free(hbuf);
     return rc;
   }
   char* h = (char*)(uintptr_t)hbuf;
@@ -712,8 +732,8 @@ static int copy_regions_impl(TsbCtx* ctx, int stream, const TsbRegion* regions, 
   }
   if (p.done == nullptr && cudaEventCreateWithFlags(&p.done, cudaEventDisableTiming) != cudaSuccess) {
     cudaStreamSynchronize(s);
-    ctx->host_arena->free(hbuf);
-    ctx->dev_arena->free(dbuf);
+    ctx->scratch_host->free(hbuf);
+    ctx->scratch_dev->free(dbuf);
     return set_err(TSB_ECUDA, "cudaEventCreate failed");
   }
   cudaEventRecord(p.done, s);

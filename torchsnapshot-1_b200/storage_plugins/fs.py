@@ -10,6 +10,7 @@ aiofiles, and the optional `read_into` lets the scheduler read straight into pin
 import asyncio
 import io
 import os
+import threading
 from concurrent.futures import ThreadPoolExecutor
 from typing import Any, Dict, Optional, Set, Tuple
 
@@ -25,9 +26,13 @@ class FSStoragePlugin(StoragePlugin):
         self._executor = ThreadPoolExecutor(
             max_workers=int(os.environ.get("TSB200_IO_CONCURRENCY", "32")), thread_name_prefix="tsb-fs"
         )
-        # pwrite/pread workers per file; up to 32 files are in flight, and 16-32 threads in total already
-        # saturate tmpfs on the measured box (profiles/r01_box_peaks.json)
-        self._io_threads = knobs.get_io_threads() or 1
+        # TSB200_IO_THREADS pins the pwrite/pread workers per file; by default they follow the load
+        self._io_threads = knobs.get_io_threads()
+        from ..scheduler import io_concurrency
+
+        self._thread_budget = io_concurrency()
+        self._inflight = 0
+        self._lock = threading.Lock()
 
     def _prepare(self, rel: str) -> str:
         path = os.path.join(self.root, rel)
@@ -37,10 +42,25 @@ class FSStoragePlugin(StoragePlugin):
             self._dir_cache.add(parent)
         return path
 
+    def _threads_for_one_op(self) -> int:
+        """Workers for one file operation: the rank's I/O thread budget split over the operations in
+        flight, so 32 concurrent slab writes use one thread each and a lone 512 MiB read uses eight."""
+        if self._io_threads:
+            return self._io_threads
+        with self._lock:
+            inflight = max(self._inflight, 1)
+        return max(1, min(8, self._thread_budget // inflight))
+
     def _write_sync(self, path: str, buf: Any) -> None:
         n = len(buf)
         addr = readonly_buffer_address(buf) if n else 0
-        _native.file_write(path, addr, n, self._io_threads)
+        with self._lock:
+            self._inflight += 1
+        try:
+            _native.file_write(path, addr, n, self._threads_for_one_op())
+        finally:
+            with self._lock:
+                self._inflight -= 1
 
     async def write(self, write_io: WriteIO) -> None:
         path = self._prepare(write_io.path)
@@ -58,7 +78,13 @@ class FSStoragePlugin(StoragePlugin):
                 raise AssertionError(f"{path}: destination holds {len(out)} bytes, the read is {n} bytes.")
             dst = out
         if n:
-            _native.file_read(path, offset, buffer_address(dst), n, self._io_threads)
+            with self._lock:
+                self._inflight += 1
+            try:
+                _native.file_read(path, offset, buffer_address(dst), n, self._threads_for_one_op())
+            finally:
+                with self._lock:
+                    self._inflight -= 1
         return dst
 
     async def read(self, read_io: ReadIO) -> None:
