@@ -347,7 +347,7 @@ class Snapshot:
     ) -> None:
         if stateful is None:
             return
-        manifest, merged_sd = get_manifest_for_rank(self.metadata, rank)
+        manifest, merged_sd = self._manifest_for_rank(rank)
         # load straight into the tensors the stateful already owns (no second copy of the state)
         _, flattened = flatten(stateful.state_dict(), prefix=key)
         flattened = {k: v for k, v in flattened.items() if isinstance(v, torch.Tensor) or _is_sharded_tensor(v)}
@@ -443,6 +443,16 @@ class Snapshot:
         storage.sync_close(event_loop=event_loop)
         event_loop.close()
         return fut.obj
+
+    def _manifest_for_rank(self, rank: int) -> Tuple[Manifest, Dict[str, ShardedTensorEntry]]:
+        """Per-rank view of the manifest, computed once per Snapshot object and rank (a restore with several
+        statefuls would otherwise re-partition the whole manifest for each of them).  Callers get a shallow
+        copy: `_load_stateful` adds elastic sharded entries to it."""
+        cache = self.__dict__.setdefault("_rank_views", {})
+        if rank not in cache:
+            cache[rank] = get_manifest_for_rank(self.metadata, rank)
+        manifest, merged = cache[rank]
+        return dict(manifest), merged
 
     # ------------------------------------------------------------------------------------------
     # metadata
