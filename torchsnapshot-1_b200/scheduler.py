@@ -62,6 +62,19 @@ def io_concurrency() -> int:
         return _MAX_PER_RANK_IO_CONCURRENCY
     cores = os.cpu_count() or 8
     return max(4, min(_MAX_PER_RANK_IO_CONCURRENCY, 2 * cores // _local_world_size))
+
+
+def read_concurrency() -> int:
+    """Storage READS in flight for this rank.  A read's bytes are useless to the device until the whole
+    request is in pinned memory, so the read side wants few requests in flight with several pread workers
+    each (the first H2D starts after one request's worth of reading, not after `io_concurrency()` requests'
+    worth).  Measured on the 9.35 GB DDP state (scripts/restore_concurrency_sweep.py): 32 in flight 34.2 GB/s,
+    3-16 in flight 36.5-38.2 GB/s, 2 in flight 29-37 GB/s.  TSB200_READ_CONCURRENCY overrides."""
+    if "TSB200_READ_CONCURRENCY" in os.environ:
+        return max(int(os.environ["TSB200_READ_CONCURRENCY"]), 1)
+    return min(io_concurrency(), 6)
+
+
 _TRACE_READS = os.environ.get("TSB200_TRACE_READS") == "1"
 _STAGING_ALIGN = 512  # each file's bytes start 512-B aligned inside the device staging block
 
@@ -479,7 +492,7 @@ async def execute_read_reqs(
 ) -> None:
     loop = asyncio.get_running_loop()
     executor = ThreadPoolExecutor(max_workers=_MAX_PER_RANK_CPU_CONCURRENCY, thread_name_prefix="tsb-consume")
-    io_slots = asyncio.Semaphore(io_concurrency())
+    io_slots = asyncio.Semaphore(read_concurrency())
     alloc = _Allocator(memory_budget_bytes)
     global last_read_stats
     rstats = _ReadStats()

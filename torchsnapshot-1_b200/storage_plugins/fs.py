@@ -49,7 +49,7 @@ class FSStoragePlugin(StoragePlugin):
             return self._io_threads
         with self._lock:
             inflight = max(self._inflight, 1)
-        return max(1, min(8, self._thread_budget // inflight))
+        return max(1, min(int(os.environ.get("TSB200_IO_THREADS_MAX", "8")), self._thread_budget // inflight))
 
     def _write_sync(self, path: str, buf: Any) -> None:
         n = len(buf)
