@@ -43,7 +43,7 @@ for trial in range(NT):
     print(json.dumps({"trial":trial,"take_ms":round(1e3*(t1-t0),1),"GBps":round(P/(t1-t0)/1e9,2),"exec_begin":rel(st.begin),"pack_launched":rel(st.pack_launched),
       "staging_done":rel(st.staging_done),"d2h_done":rel(st.d2h_done),"writes_done":rel(st.writes_done),"device_ms":round(st.device_ms(),1),"kernel_ms":round(st.kernel_ms(),2)}),flush=True)
     if prof:
-        s=io.StringIO(); pstats.Stats(prof,stream=s).sort_stats("cumulative").print_stats(25); print(s.getvalue()[:3500])
+        s=io.StringIO(); pstats.Stats(prof,stream=s).sort_stats(os.environ.get("PROF_SORT","cumulative")).print_stats(int(os.environ.get("PROF_N","25"))); print(s.getvalue()[:int(os.environ.get("PROF_CHARS","3500"))])
     prof = cProfile.Profile() if (trial==3 and NT==4) else None
     t0=time.monotonic()
     if prof: prof.enable()
@@ -52,7 +52,7 @@ for trial in range(NT):
     t1=time.monotonic(); rs=scheduler.last_read_stats
     print(json.dumps({"trial":trial,"restore_ms":round(1e3*(t1-t0),1),"GBps":round(P/(t1-t0)/1e9,2),"read_begin":round(1e3*(rs.begin-t0),1),"unpack_ms":round(rs.unpack_ms,2)}),flush=True)
     if prof:
-        s=io.StringIO(); pstats.Stats(prof,stream=s).sort_stats("cumulative").print_stats(25); print(s.getvalue()[:3500])
+        s=io.StringIO(); pstats.Stats(prof,stream=s).sort_stats(os.environ.get("PROF_SORT","cumulative")).print_stats(int(os.environ.get("PROF_N","25"))); print(s.getvalue()[:int(os.environ.get("PROF_CHARS","3500"))])
     if rs.trace and trial==NT-1:
         tr=sorted(rs.trace, key=lambda x:x[1])
         import statistics

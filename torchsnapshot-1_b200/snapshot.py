@@ -313,6 +313,10 @@ class Snapshot:
     # restore / read_object
     # ------------------------------------------------------------------------------------------
     def restore(self, app_state: AppState) -> None:
+        with _gc_paused():  # same reason as in take: planning allocates a few objects per tensor
+            self._restore_impl(app_state)
+
+    def _restore_impl(self, app_state: AppState) -> None:
         _validate_app_state(app_state)
         event_loop = asyncio.new_event_loop()
         pg = PGWrapper(self.pg)
