@@ -14,6 +14,17 @@ outs = StateDict({k: torch.empty_like(v) for k, v in state.items()})
 base = [tempfile.mkdtemp(dir="/dev/shm") if rank == 0 else None]; dist.broadcast_object_list(base, src=0); base = base[0]
 snap = Snapshot.take(os.path.join(base, "s"), {"ddp": StateDict(state)}, replicated=["**"])
 def sync(): torch.cuda.synchronize(); dist.barrier(device_ids=[lr])
+SWEEP = [(None, 8)] + [(c, t) for c in (2, 4, 6, 8, 16) for t in (2, 4, 8)] if os.environ.get("SWEEP") == "1" else []
+for conc, tmax in SWEEP:
+    if conc is None: os.environ.pop("TSB200_READ_CONCURRENCY", None)
+    else: os.environ["TSB200_READ_CONCURRENCY"] = str(conc)
+    os.environ["TSB200_IO_THREADS_MAX"] = str(tmax)
+    ms = []
+    for _ in range(3):
+        sync(); t0 = time.monotonic(); snap.restore({"ddp": outs}); sync(); ms.append(round(1e3 * (time.monotonic() - t0), 1))
+    rd = [None] * world; dist.all_gather_object(rd, round(reshard.last_stats.phase_ms["read"], 1))
+    if rank == 0: print(json.dumps({"read_concurrency": conc, "threads_max": tmax, "restore_ms": ms, "best_GBps": round(P / min(ms) / 1e6, 2), "read_phase_ms_last": rd}), flush=True)
+os.environ.pop("TSB200_READ_CONCURRENCY", None); os.environ.pop("TSB200_IO_THREADS_MAX", None)
 for trial in range(4):
     sync(); t0 = time.monotonic()
     snap.restore({"ddp": outs})

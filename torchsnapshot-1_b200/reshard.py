@@ -312,9 +312,9 @@ def p2p_restore_units(
         async def read_all() -> None:
             loop = asyncio.get_running_loop()
             alloc = _Allocator()
-            from .scheduler import io_concurrency
+            from .scheduler import read_concurrency
 
-            sem = asyncio.Semaphore(io_concurrency())
+            sem = asyncio.Semaphore(read_concurrency())
 
             async def one(key: UnitKey) -> None:
                 nbytes = sizes[key]
