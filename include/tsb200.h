@@ -243,12 +243,18 @@ int tsb_peer_enable(TsbCtx* ctx, int peer_device);
 
 /* ---- storage sink fast path (behind the unchanged StoragePlugin ABI) ------ */
 
+/* File flags.  TSB_FILE_DIRECT: the 4 KiB-aligned body of the transfer bypasses the page cache
+ * (O_DIRECT) when `hptr` and the file offset are 4 KiB aligned -- pinned arena blocks are; the
+ * sub-page tail, unaligned requests and file systems without O_DIRECT use the buffered path, so the
+ * bytes on disk never depend on the flag. */
+#define TSB_FILE_DIRECT 1u
+
 /* Write `nbytes` at `hptr` to a new file `path` (parents must exist) with `nthreads` parallel
  * pwrite workers (0 = library default).  Replaces the aiofiles write of FSStoragePlugin.write
  * (storage_plugins/fs.py:26-36). */
-int tsb_file_write(const char* path, const void* hptr, uint64_t nbytes, int nthreads);
+int tsb_file_write(const char* path, const void* hptr, uint64_t nbytes, int nthreads, uint32_t flags);
 /* Read `nbytes` at `offset` of `path` into `hptr` (FSStoragePlugin.read, fs.py:38-49). */
-int tsb_file_read(const char* path, uint64_t offset, void* hptr, uint64_t nbytes, int nthreads);
+int tsb_file_read(const char* path, uint64_t offset, void* hptr, uint64_t nbytes, int nthreads, uint32_t flags);
 
 #ifdef __cplusplus
 }

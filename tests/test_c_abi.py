@@ -64,3 +64,39 @@ def test_host_helpers(tmp_path):
     assert np.array_equal(back, src[12345 : 12345 + (1 << 20)])
     with pytest.raises(_native.TsbError):
         _native.file_read(str(tmp_path / "missing"), 0, back.ctypes.data, 16, 1)
+
+
+def test_file_direct_flag_never_changes_the_bytes(tmp_path):
+    # TSB_FILE_DIRECT moves the page-aligned body with O_DIRECT where the file system takes it and falls
+    # back to the buffered path otherwise (tmpfs, unaligned buffers / offsets, the sub-page tail)
+    import mmap
+
+    import numpy as np
+
+    n = (5 << 20) + 777
+    payload = np.random.RandomState(1).randint(0, 256, size=n).astype(np.uint8)
+    page = mmap.mmap(-1, n + 4096)  # page-aligned, like a pinned arena block
+    aligned = np.frombuffer(page, dtype=np.uint8, count=n)
+    aligned[:] = payload
+    for root in (str(tmp_path), "/dev/shm"):
+        for name, arr in (("aligned", aligned), ("unaligned", np.frombuffer(page, dtype=np.uint8, count=n - 1, offset=1))):
+            path = os.path.join(root, f"tsb_direct_{os.getpid()}_{name}.bin")
+            try:
+                _native.file_write(path, arr.ctypes.data, arr.nbytes, 3, _native.FILE_DIRECT)
+                with open(path, "rb") as f:
+                    assert f.read() == arr.tobytes()
+                back_page = mmap.mmap(-1, n + 4096)
+                back = np.frombuffer(back_page, dtype=np.uint8, count=1 << 20)
+                for off in (0, 4096 * 3, 12345):
+                    back[:] = 0
+                    _native.file_read(path, off, back.ctypes.data, back.nbytes, 2, _native.FILE_DIRECT)
+                    assert np.array_equal(back, arr[off : off + (1 << 20)])
+                del back
+                back_page.close()
+            finally:
+                if os.path.exists(path):
+                    os.remove(path)
+    with pytest.raises(_native.TsbError):
+        _native.file_write(str(tmp_path / "x"), aligned.ctypes.data, 16, 1, 0x80)
+    del aligned, arr
+    page.close()

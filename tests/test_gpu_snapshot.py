@@ -66,8 +66,11 @@ def test_c1_on_gpu_matches_reference_snapshot(golden_dir, tmp_path, engine):
     assert _bytes(st[2]["exp_avg_sq"]) == oracle.serialize(inputs["tensors"]["optim/state/2/exp_avg_sq"])
 
 
+@pytest.mark.parametrize("fs_direct", ["0", "1"])
 @pytest.mark.parametrize("case", ["mixed", "threshold"])
-def test_gpu_take_matches_reference_fixture(golden_dir, tmp_path, case):
+def test_gpu_take_matches_reference_fixture(golden_dir, tmp_path, case, fs_direct, monkeypatch):
+    # fs_direct=1: the FS plugin moves the page-aligned body of each file with O_DIRECT; bytes are the same
+    monkeypatch.setenv("TSB200_FS_DIRECT", fs_direct)
     gold = json.load(open(os.path.join(golden_dir, f"slab_{case}.json")))
     threshold, items = getattr(_cases, f"slab_case_{case}")()
     state = StateDict({p: _cases.build_view(spec, "cuda") for p, spec in items})

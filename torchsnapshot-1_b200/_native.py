@@ -82,8 +82,8 @@ _SIGNATURES = {
     "tsb_ipc_open": (_i, [_p, _p, ctypes.POINTER(_u64)]),
     "tsb_ipc_close": (_i, [_p, _u64]),
     "tsb_peer_enable": (_i, [_p, _i]),
-    "tsb_file_write": (_i, [ctypes.c_char_p, _p, _u64, _i]),
-    "tsb_file_read": (_i, [ctypes.c_char_p, _u64, _p, _u64, _i]),
+    "tsb_file_write": (_i, [ctypes.c_char_p, _p, _u64, _i, ctypes.c_uint32]),
+    "tsb_file_read": (_i, [ctypes.c_char_p, _u64, _p, _u64, _i, ctypes.c_uint32]),
 }
 
 _lib: Optional[ctypes.CDLL] = None
@@ -283,11 +283,14 @@ def host_memcpy(dst: int, src: int, nbytes: int, nthreads: int = 0) -> None:
     _check(lib, lib.tsb_host_memcpy(dst, src, nbytes, nthreads))
 
 
-def file_write(path: str, hptr: int, nbytes: int, nthreads: int = 0) -> None:
-    lib = load_library()
-    _check(lib, lib.tsb_file_write(os.fsencode(path), hptr, nbytes, nthreads))
+FILE_DIRECT = 1  # TSB_FILE_DIRECT
 
 
-def file_read(path: str, offset: int, hptr: int, nbytes: int, nthreads: int = 0) -> None:
+def file_write(path: str, hptr: int, nbytes: int, nthreads: int = 0, flags: int = 0) -> None:
     lib = load_library()
-    _check(lib, lib.tsb_file_read(os.fsencode(path), offset, hptr, nbytes, nthreads))
+    _check(lib, lib.tsb_file_write(os.fsencode(path), hptr, nbytes, nthreads, flags))
+
+
+def file_read(path: str, offset: int, hptr: int, nbytes: int, nthreads: int = 0, flags: int = 0) -> None:
+    lib = load_library()
+    _check(lib, lib.tsb_file_read(os.fsencode(path), offset, hptr, nbytes, nthreads, flags))

@@ -60,6 +60,12 @@ def trim_arenas_after_use() -> bool:
     return os.getenv("TSB200_TRIM_ARENAS", "0").lower() in ("1", "true")
 
 
+def is_fs_direct_enabled() -> bool:
+    """TSB200_FS_DIRECT=1: the FS plugin moves the 4 KiB-aligned body of every file transfer with O_DIRECT
+    (no page-cache copy, no dirty-page throttling) -- for checkpoints onto real block devices."""
+    return os.getenv("TSB200_FS_DIRECT", "0").lower() in ("1", "true")
+
+
 def get_io_threads() -> int:
     return _int_env(_IO_THREADS_ENV_VAR, 0)
 

@@ -33,6 +33,9 @@ class FSStoragePlugin(StoragePlugin):
         self._thread_budget = io_concurrency()
         self._inflight = 0
         self._lock = threading.Lock()
+        # TSB200_FS_DIRECT=1: page-cache bypass (O_DIRECT) for the aligned body of every transfer -- for real
+        # block devices; tmpfs has no use for it
+        self._flags = _native.FILE_DIRECT if knobs.is_fs_direct_enabled() else 0
 
     def _prepare(self, rel: str) -> str:
         path = os.path.join(self.root, rel)
@@ -57,7 +60,7 @@ class FSStoragePlugin(StoragePlugin):
         with self._lock:
             self._inflight += 1
         try:
-            _native.file_write(path, addr, n, self._threads_for_one_op())
+            _native.file_write(path, addr, n, self._threads_for_one_op(), self._flags)
         finally:
             with self._lock:
                 self._inflight -= 1
@@ -81,7 +84,7 @@ class FSStoragePlugin(StoragePlugin):
             with self._lock:
                 self._inflight += 1
             try:
-                _native.file_read(path, offset, buffer_address(dst), n, self._threads_for_one_op())
+                _native.file_read(path, offset, buffer_address(dst), n, self._threads_for_one_op(), self._flags)
             finally:
                 with self._lock:
                     self._inflight -= 1
