@@ -56,7 +56,8 @@ def run(name, boxes, p2p):
         mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX); sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
         res.update({"copy_ms_max": round(mx[0].item(), 3), "peer_GB_total": round(sm[1].item() / 1e9, 3), "local_GB_total": round(sm[2].item() / 1e9, 3),
                     "storage_read_GB_total": round(sm[3].item() / 1e9, 3),
-                    "nvlink_GBps_per_gpu_in": round(mx[1].item() / max(mx[0].item(), 1e-9) / 1e6, 1)})
+                    "nvlink_GBps_per_gpu_in": round(mx[1].item() / max(mx[0].item(), 1e-9) / 1e6, 1),
+                    "rank0_phases_ms_last": {k: round(v, 1) for k, v in st.phase_ms.items()}})
     else:
         res["storage_read_GB_total"] = "every rank reads every overlapping piece"
     if rank == 0: print(json.dumps(res), flush=True)

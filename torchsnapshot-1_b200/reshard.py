@@ -256,6 +256,7 @@ def p2p_restore_units(
     blocks: List[int] = []  # device arena blocks to free at the end
     opened: Dict[Tuple[int, bytes], int] = {}
     executor = ThreadPoolExecutor(max_workers=4, thread_name_prefix="tsb-reshard")
+    ipc_executor = ThreadPoolExecutor(max_workers=8, thread_name_prefix="tsb-ipc")
     try:
         # ---- staging for the units this rank owns: ONE block when the arena allows it, so that every
         # peer maps a single IPC handle (cudaIpcOpenMemHandle costs milliseconds per handle) ----------
@@ -288,7 +289,19 @@ def p2p_restore_units(
         stats.phase_ms["plan"] = 1e3 * (t_read - t_begin)
         regions: List[RegionTuple] = []
 
+        def open_peer(hk: Tuple[int, bytes]) -> None:
+            t0 = time.monotonic()
+            opened[hk] = ctx.ipc_open(hk[1])
+            stats.phase_ms["ipc_open"] = stats.phase_ms.get("ipc_open", 0.0) + 1e3 * (time.monotonic() - t0)
+
         async def build_regions() -> None:
+            loop = asyncio.get_running_loop()
+            # mapping a peer's staging block costs milliseconds per GiB: do it on worker threads, all peers
+            # at once, while the event loop keeps the storage reads and H2D copies going
+            wanted = {(owners[key], all_exports[owners[key]][key][0]) for key, unit in mine_by_key.items()
+                      if owners.get(key) is not None and owners[key] != rank and unit.need}
+            if wanted:
+                await asyncio.gather(*(loop.run_in_executor(ipc_executor, open_peer, hk) for hk in sorted(wanted)))
             n = 0
             for key, unit in mine_by_key.items():
                 owner = owners.get(key)
@@ -299,10 +312,7 @@ def p2p_restore_units(
                     stats.local_bytes += unit.need
                 else:
                     handle, offset = all_exports[owner][key]
-                    hk = (owner, handle)
-                    if hk not in opened:
-                        opened[hk] = ctx.ipc_open(handle)
-                    src_base = opened[hk] + offset
+                    src_base = opened[(owner, handle)] + offset
                     stats.peer_bytes += unit.need
                 regions.extend(unit.regions(src_base))
                 n += 1
@@ -377,6 +387,7 @@ def p2p_restore_units(
         stats.phase_ms["barrier"] = 1e3 * (time.monotonic() - t_end)
     finally:
         executor.shutdown(wait=False)
+        ipc_executor.shutdown(wait=True)
         for base_addr in opened.values():
             try:
                 ctx.ipc_close(base_addr)
