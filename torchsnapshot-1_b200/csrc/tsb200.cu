@@ -202,6 +202,9 @@ class Arena {
       if (m != MAP_FAILED) {
         char* q = (char*)(((uintptr_t)m + huge - 1) & ~(uintptr_t)(huge - 1));
         (void)madvise(q, n, MADV_HUGEPAGE);
+        // like driver-allocated pinned memory, the segment is not inherited by forked children (data-loader
+        // workers): no copy-on-write can ever move a page the DMA engines are writing to
+        (void)madvise(q, n, MADV_DONTFORK);
         unsigned hw = std::thread::hardware_concurrency();
         int nthreads = (int)std::min<uint64_t>(std::min<unsigned>(hw ? hw : 4, 16), std::max<uint64_t>(n >> 26, 1));
         const uint64_t per = ((n + nthreads - 1) / nthreads + 4095) & ~4095ull;
