@@ -300,3 +300,58 @@ def test_tma_and_lsu_variants_of_the_flat_kernel(golden_dir, monkeypatch, use_tm
         assert sha(_to_host(slab)) == gold["slabs"][0]["sha256"]
     finally:
         engmod.shutdown_engines()
+
+
+def _fill_pattern(t: torch.Tensor, seed: int) -> None:
+    # cheap, position-dependent bytes for multi-GiB buffers (a 256 MiB random block repeated with a twist
+    # per repetition, so a copy that lands 2^32 bytes off does not go unnoticed)
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    block = torch.randint(0, 256, (256 << 20,), dtype=torch.uint8, device="cuda", generator=g)
+    n = t.numel()
+    for i, lo in enumerate(range(0, n, block.numel())):
+        hi = min(n, lo + block.numel())
+        t[lo:hi] = block[: hi - lo] + (i * 37 & 0xFF)
+
+
+def test_regions_beyond_4GiB(engine):
+    """Maximum sizes: 64-bit byte arithmetic inside ONE region -- a flat run longer than 4 GiB from an odd
+    address, long pitched rows spanning more than 4 GiB of source, and short runs whose flat payload
+    offset passes 2^32.  Compared on the device against torch's own indexing of the same bytes."""
+    free, _ = torch.cuda.mem_get_info()
+    if free < (24 << 30):
+        pytest.skip("needs 24 GiB of free device memory")
+    # (1) flat: 4 GiB + 4099 bytes, source at an odd address, destination 3 bytes into its buffer
+    n = (4 << 30) + 4099
+    src = torch.empty(5_500_000_001, dtype=torch.uint8, device="cuda")
+    _fill_pattern(src, 1)
+    dst = torch.zeros(n + 8, dtype=torch.uint8, device="cuda")
+    _launch(engine, [(src.data_ptr() + 1, dst.data_ptr() + 3, n, (), (), ())])
+    assert torch.equal(dst[3 : 3 + n], src[1 : 1 + n])
+    assert int(dst[:3].sum()) == 0 and int(dst[3 + n :].sum()) == 0
+    del dst
+    # (2) long runs: 40 000 rows of 64 KiB taken from rows 128 KiB apart (source span 5.2 GB)
+    rows, run, pitch = 40000, 64 << 10, 128 << 10
+    assert rows * pitch <= src.numel() - 1 and rows * pitch > (4 << 30)
+    view = src[1 : 1 + rows * pitch].view(rows, pitch)[:, 100 : 100 + run]
+    out = torch.zeros(rows * run + 16, dtype=torch.uint8, device="cuda")
+    _launch(engine, pack_regions(view, out.data_ptr() + 7))
+    assert torch.equal(out[7 : 7 + rows * run].view(rows, run), view)
+    assert int(out[:7].sum()) == 0 and int(out[7 + rows * run :].sum()) == 0
+    del out, view
+    # (3) short runs: 32-byte runs every 48 bytes; 90 M rows -> payload 2.9 GB from a 4.3 GB span, and
+    # scattered back (unpack) into a 4.3 GB span: flat offsets and strides x index products pass 2^32
+    rows, run, pitch = 90_000_000, 32, 48
+    assert rows * pitch > (4 << 30) and rows * pitch <= src.numel() - 1
+    view = src[1 : 1 + rows * pitch].view(rows, pitch)[:, 8 : 8 + run]
+    packed = torch.zeros(rows * run, dtype=torch.uint8, device="cuda")
+    _launch(engine, pack_regions(view, packed.data_ptr()))
+    assert torch.equal(packed.view(rows, run)[-1000:], view[-1000:])  # the tail lies beyond 2^32 on both sides
+    step = 9_000_000
+    for lo in range(0, rows, step):
+        assert torch.equal(packed.view(rows, run)[lo : lo + step], view[lo : lo + step])
+    back = torch.zeros(rows * pitch, dtype=torch.uint8, device="cuda")
+    back_v = back.view(rows, pitch)[:, 8 : 8 + run]
+    _launch(engine, unpack_regions(packed.data_ptr(), back_v))
+    for lo in range(0, rows, step):
+        assert torch.equal(back_v[lo : lo + step], view[lo : lo + step])
+    assert int(back.view(rows, pitch)[:, :8].sum()) == 0 and int(back.view(rows, pitch)[:, 8 + run :].sum()) == 0
