@@ -41,6 +41,8 @@ from .manifest import (
 )
 from .regions import RegionTuple, box_regions, contiguous_strides, pack_regions, unpack_regions
 from .serialization import (
+    tensor_as_memoryview,
+    tensor_from_memoryview,
     _BUFFER_PROTOCOL_SET as _BUFFER_PROTOCOL_DTYPES,
     _DTYPE_TO_STRING as _DTYPE_STRINGS,
     _STRING_TO_DTYPE as _STRING_DTYPES,
@@ -81,30 +83,6 @@ async def _run_in_executor(executor: Optional[Executor], func: Callable[..., Any
 # ----------------------------------------------------------------------------------------------
 # host-side byte views (CPU tensors only)
 # ----------------------------------------------------------------------------------------------
-def tensor_as_memoryview(tensor: torch.Tensor) -> memoryview:
-    """Zero-copy byte view of a CPU tensor in the payload layout (reference serialization.py:162-188).
-
-    Unlike the reference, bf16 tensors with an odd element count keep their last element (the
-    reference drops two bytes there).
-    """
-    if not is_buffer_protocol_dtype(tensor.dtype):
-        raise ValueError(f"tensor_as_memoryview() doesn't support the dtype {tensor.dtype}.")
-    if tensor.device != torch.device("cpu"):
-        raise ValueError("tensor_as_memoryview() only accepts CPU tensors.")
-    flat = tensor.detach().contiguous().reshape(-1)
-    return memoryview(flat.view(torch.uint8).numpy()).cast("b")
-
-
-# tensors made from read-only buffers are intermediate, read-only views (reference serialization.py:236-244)
-warnings.filterwarnings("ignore", message="The given buffer is not writable")
-
-
-def tensor_from_memoryview(mv: BufferType, dtype: torch.dtype, shape: Sequence[int]) -> torch.Tensor:
-    if len(mv) == 0:
-        return torch.empty(list(shape), dtype=dtype)
-    return torch.frombuffer(mv, dtype=dtype).reshape(list(shape))
-
-
 def tensor_copy(dst: torch.Tensor, src: torch.Tensor) -> None:
     """dst <- src with the reference's quantization rule (tensor.py:383-403)."""
     if src.is_quantized and (not dst.is_quantized or dst.qscheme() != src.qscheme() or dst.dtype != src.dtype):

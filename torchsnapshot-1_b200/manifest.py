@@ -167,6 +167,14 @@ class PrimitiveEntry(Entry):
 
 Manifest = Dict[str, Entry]
 
+try:  # loader for metadata files written as real yaml (reference manifest.py:20-25)
+    from yaml import CSafeLoader as Loader
+except ImportError:  # pragma: no cover
+    try:
+        from yaml import SafeLoader as Loader
+    except ImportError:
+        Loader = None
+
 _esc = json.encoder.encode_basestring_ascii  # C implementation; same escaping as json.dumps
 
 
@@ -303,15 +311,19 @@ class SnapshotMetadata:
         )
 
     @classmethod
-    def from_yaml(cls, text: str) -> "SnapshotMetadata":
+    def from_yaml(cls, yaml_str: str) -> "SnapshotMetadata":
         try:
-            doc = json.loads(text)
+            doc = json.loads(yaml_str)  # what to_yaml() has written since the reference switched to json
         except json.JSONDecodeError:
             import yaml  # legacy snapshots written as real yaml
 
-            doc = yaml.safe_load(text)
+            doc = yaml.load(yaml_str, Loader=Loader if Loader is not None else yaml.SafeLoader)
         manifest = {path: entry_from_obj(o) for path, o in doc["manifest"].items()}
         return cls(version=doc["version"], world_size=doc["world_size"], manifest=manifest)
+
+
+def is_dict_entry(entry: Any) -> bool:
+    return getattr(entry, "type", None) in ("dict", "OrderedDict")
 
 
 def is_container_entry(entry: Any) -> bool:

@@ -173,3 +173,11 @@ def consolidate_replicated_entries(rank_to_entries: List[Dict[str, Entry]], dedu
             continue
         entries.update(replicated)
     return rank_to_entries
+
+
+def consolidate_replicated_entries_dist(entries: Dict[str, Entry], pg: Any, dedup: bool = True) -> Dict[str, Entry]:
+    """Collective form of `consolidate_replicated_entries` (reference partitioner.py:306-316): gather every
+    rank's entries, consolidate, keep this rank's."""
+    gathered: List[Any] = [None] * pg.get_world_size()
+    pg.all_gather_object(obj_list=gathered, obj=entries)
+    return consolidate_replicated_entries(rank_to_entries=gathered, dedup=dedup)[pg.get_rank()]

@@ -54,6 +54,9 @@ from .scheduler import (
     sync_execute_read_reqs,
     sync_execute_write_reqs,
 )
+from .manifest_ops import get_manifest_for_rank, handle_sharded_tensor_elasticity
+from .state_dict import StateDict  # noqa: F401  (re-exported: `from ...snapshot import Snapshot, StateDict`)
+from .stateful import AppState
 from .storage_plugin import url_to_storage_plugin
 
 logger: logging.Logger = logging.getLogger(__name__)
@@ -61,18 +64,6 @@ logger: logging.Logger = logging.getLogger(__name__)
 SNAPSHOT_METADATA_FNAME = ".snapshot_metadata"
 VERSION = "0.1.0"  # the metadata schema version the reference writes (torchsnapshot/version.py:17)
 
-AppState = Dict[str, Any]
-
-
-class StateDict(dict):
-    """dict that is its own state dict (reference state_dict.py:13-41)."""
-
-    def state_dict(self) -> Dict[str, Any]:
-        return dict(self)
-
-    def load_state_dict(self, state_dict: Dict[str, Any]) -> None:
-        self.clear()
-        self.update(state_dict)
 
 
 def _validate_app_state(app_state: AppState) -> None:
@@ -189,6 +180,15 @@ class Snapshot:
             )
         return PendingSnapshot(path, pending, pg_wrapper, metadata, storage, event_loop, storage_options)
 
+    @staticmethod
+    def _coalesce_replicated(global_replicated: List[List[str]]) -> Set[str]:
+        """Only globs every rank named are replicated (reference snapshot.py:809-812)."""
+        return set.intersection(*map(set, global_replicated))
+
+    @staticmethod
+    def _infer_replicated(replicated: List[str], app_state: AppState) -> List[str]:
+        return _infer_replicated(replicated, app_state)
+
     @classmethod
     def _take_impl(
         cls,
@@ -210,7 +210,7 @@ class Snapshot:
         if hello[0][0] != path:
             logger.warning(f"Rank {rank} specified a path ({path}) different from rank 0 ({hello[0][0]}).")
         path = hello[0][0]
-        globs = set.intersection(*(set(h[1]) for h in hello))
+        globs = cls._coalesce_replicated([h[1] for h in hello])
         global_keys = sorted(set(itertools.chain.from_iterable(h[2] for h in hello)))
         local_world = sum(1 for h in hello if h[3] == hello[rank][3])
         set_local_world_size(local_world)
@@ -355,10 +355,9 @@ class Snapshot:
         # load straight into the tensors the stateful already owns (no second copy of the state)
         _, flattened = flatten(stateful.state_dict(), prefix=key)
         flattened = {k: v for k, v in flattened.items() if isinstance(v, torch.Tensor) or _is_sharded_tensor(v)}
-        # a rank that did not exist at save time still gets the sharded entries it asks for
-        for logical_path in flattened:
-            if logical_path not in manifest and logical_path in merged_sd:
-                manifest[logical_path] = merged_sd[logical_path]
+        # sharded tensors follow what this state dict asks for: requested ones this rank did not save are
+        # added, saved ones nobody asks for are dropped
+        handle_sharded_tensor_elasticity(manifest, merged_sd, list(flattened.keys()))
         prefix = _encode(key)
         containers: Manifest = {}
         read_reqs: List[ReadReq] = []
@@ -487,35 +486,6 @@ class Snapshot:
         )
 
 
-def get_manifest_for_rank(metadata: SnapshotMetadata, rank: int) -> Tuple[Manifest, Dict[str, ShardedTensorEntry]]:
-    """The view of the global manifest a rank restores from (reference manifest_ops.py:24-115):
-    its own entries plus the replicated ones (listed under rank 0); sharded entries merged over all
-    ranks; a rank that did not exist at save time sees the replicated entries only."""
-    per_rank: List[Manifest] = [{} for _ in range(metadata.world_size)]
-    for path, entry in metadata.manifest.items():
-        r, _, logical_path = path.partition("/")
-        per_rank[int(r)][logical_path] = entry
-    shards_by_path: Dict[str, List[Any]] = defaultdict(list)
-    for m in per_rank:
-        for logical_path, entry in m.items():
-            if isinstance(entry, ShardedTensorEntry):
-                shards_by_path[logical_path] += entry.shards
-    merged = {
-        p: ShardedTensorEntry(shards=sorted(shards, key=lambda s: s.offsets)) for p, shards in shards_by_path.items()
-    }
-    if rank < metadata.world_size:
-        local = dict(per_rank[rank])
-        for logical_path, entry in per_rank[0].items():
-            if is_replicated(entry):
-                local[logical_path] = entry
-        for logical_path, entry in list(local.items()):
-            if isinstance(entry, ShardedTensorEntry):
-                local[logical_path] = merged[logical_path]
-    else:
-        local = {p: e for p, e in per_rank[0].items() if is_container_entry(e) or is_replicated(e)}
-    return local, merged
-
-
 class PendingSnapshot:
     """Handle of an async_take: the background thread finishes D2H + storage I/O, then the ranks
     agree (through the default store, never through collectives in this thread) and rank 0
@@ -585,7 +555,13 @@ class PendingSnapshot:
     def wait(self) -> Snapshot:
         self.thread.join()
         if self.exc_info is not None:
-            raise self.exc_info[1].with_traceback(self.exc_info[2])
+            # same error type and message as the reference (snapshot.py:935-941), original as the cause
+            import traceback
+
+            formatted = "".join(traceback.format_exception(*self.exc_info))
+            raise RuntimeError(
+                f"Encountered exception while taking snapshot asynchronously:\n{formatted}"
+            ) from self.exc_info[1]
         return Snapshot(path=self.path, pg=self.pg_obj, storage_options=self._storage_options)
 
     def done(self) -> bool:
