@@ -355,3 +355,82 @@ def test_regions_beyond_4GiB(engine):
     for lo in range(0, rows, step):
         assert torch.equal(back_v[lo : lo + step], view[lo : lo + step])
     assert int(back.view(rows, pitch)[:, :8].sum()) == 0 and int(back.view(rows, pitch)[:, 8 + run :].sum()) == 0
+
+
+def _random_view(rs, base: torch.Tensor) -> torch.Tensor:
+    """A random non-overlapping view of `base`: per-dim slices with steps, then a random permutation, then
+    (sometimes) a dropped leading index -- the shapes torch hands a stager in practice, and then some."""
+    idx = []
+    for n in base.shape:
+        lo = int(rs.randint(0, max(n // 3, 1)))
+        hi = int(rs.randint(lo + 1, n + 1))
+        step = int(rs.choice([1, 1, 1, 2, 3]))
+        idx.append(slice(lo, hi, step))
+    v = base[tuple(idx)]
+    if v.ndim > 1 and rs.rand() < 0.6:
+        v = v.permute(*[int(i) for i in rs.permutation(v.ndim)])
+    if v.ndim > 1 and rs.rand() < 0.2:
+        v = v[int(rs.randint(0, v.shape[0]))]
+    return v
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_random_views_one_launch_fuzz(engine, seed):
+    """~150 random strided views of every buffer-protocol dtype, ranks 0-5, packed back to back at arbitrary
+    slab offsets by ONE launch and scattered back by ONE launch; bytes compared with the CPU oracle."""
+    rs = np.random.RandomState(1000 + seed)
+    dtypes = [torch.float32, torch.bfloat16, torch.float16, torch.float64, torch.int64, torch.int32, torch.int16,
+              torch.int8, torch.uint8, torch.bool]
+    cpu_views, gpu_views, gpu_bases, cpu_bases = [], [], [], []
+    for i in range(150):
+        rank = int(rs.randint(0, 6))
+        budget = int(2 ** rs.uniform(4, 21))  # elements in the base
+        shape = []
+        for d in range(rank):
+            n = max(1, int(round(budget ** (1.0 / (rank - d)) * rs.uniform(0.5, 1.5)))) if budget > 1 else 1
+            n = min(n, budget)
+            shape.append(n)
+            budget = max(budget // n, 1)
+        dtype = dtypes[int(rs.randint(0, len(dtypes)))]
+        base = _cases.raw_tensor(seed * 1000 + i, shape, dtype)
+        gbase = base.cuda()
+        cpu_bases.append(base)
+        gpu_bases.append(gbase)
+        if rank == 0:
+            cpu_views.append(base)
+            gpu_views.append(gbase)
+            continue
+        state = rs.get_state()
+        cpu_views.append(_random_view(rs, base))
+        rs.set_state(state)
+        gpu_views.append(_random_view(rs, gbase))
+    # slab layout: members back to back with small random gaps, so offsets have every alignment
+    offs, total = [], 3
+    for v in cpu_views:
+        offs.append(total)
+        total += v.numel() * v.element_size() + int(rs.randint(0, 4))
+    slab = torch.full((total + 16,), 0x5A, dtype=torch.uint8, device="cuda")
+    regions = []
+    for v, o in zip(gpu_views, offs):
+        regions += pack_regions(v, slab.data_ptr() + o)
+    _launch(engine, regions)
+    want = bytearray(b"\x5a" * (total + 16))
+    for v, o in zip(cpu_views, offs):
+        b = oracle.serialize(v)
+        want[o : o + len(b)] = b
+    assert _to_host(slab) == bytes(want)
+    # scatter back into marker-filled twins with the same geometry
+    twins_g, twins_c, back = [], [], []
+    for gb, cb, gv, cv, o in zip(gpu_bases, cpu_bases, gpu_views, cpu_views, offs):
+        nbytes = cb.numel() * cb.element_size()
+        tg = torch.full((nbytes,), 0xA7, dtype=torch.uint8, device="cuda").view(gb.dtype).reshape(gb.shape)
+        tc = torch.full((nbytes,), 0xA7, dtype=torch.uint8).view(cb.dtype).reshape(cb.shape)
+        vg = tg.as_strided(gv.shape, gv.stride(), gv.storage_offset())
+        vc = tc.as_strided(cv.shape, cv.stride(), cv.storage_offset())
+        back += unpack_regions(slab.data_ptr() + o, vg)
+        oracle.deserialize_into(vc, bytes(want[o : o + cv.numel() * cv.element_size()]))
+        twins_g.append(tg)
+        twins_c.append(tc)
+    _launch(engine, back)
+    for i, (tg, tc) in enumerate(zip(twins_g, twins_c)):
+        assert _to_host(tg.reshape(-1).view(torch.uint8)) == tc.reshape(-1).view(torch.uint8).numpy().tobytes(), i
