@@ -37,8 +37,9 @@
 // Strided regions whose runs are at least this long are expanded by the host into flat tiles (one
 // or more per run); shorter runs go to the strided kernel, one per warp.
 #define TSB_FLAT_RUN_MIN (8u * 1024u)
-// A run shorter than this is copied element-wise, one unit per thread.
-#define TSB_WARP_RUN_MIN 64u
+// Misaligned runs shorter than this many UNITS (the widest power of two every address of the region is
+// aligned to) are copied unit by unit, longer ones one run per warp with realignment.
+#define TSB_WARP_RUN_MIN 128u
 
 // One unit of work.  Flat tiles: src/dst are the absolute addresses of the tile's first byte.
 // Strided tiles: `region` indexes the region table and `off` is the flat payload offset.
@@ -330,13 +331,30 @@ __device__ __forceinline__ void run_offsets(const TsbRegion* __restrict__ r, uin
   }
 }
 
+// 16-byte unit load that asks L2 to fetch only the 64-byte half line on a miss.  The default promotes a miss
+// to the whole 128-byte line, which doubles the DRAM reads of a gather of 64-byte runs: pitched 64-byte rows
+// (a column shard of a 128-column fp32 table over 8 ranks) move 4.25 TB/s without the hint and 5.19 TB/s with
+// it; longer runs are unaffected, and on 1/2/4-byte units the hint costs 2-4 %, so only this width carries it
+// (scripts/strided_bench.py, scripts/strided_sweep.py; TSB200_L2_64B=0 turns it off).
+template <typename T>
+__device__ __forceinline__ T ld_unit(const T* p, bool hint64) {
+  return *p;
+}
+template <>
+__device__ __forceinline__ uint4 ld_unit<uint4>(const uint4* p, bool hint64) {
+  if (!hint64) return *p;
+  uint4 v;
+  asm volatile("ld.global.L2::64B.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
 // Unit-wise copy: unit u of the tile is element k of run q; consecutive threads take consecutive units,
 // so accesses stay coalesced within a run and across adjacent runs.  Four units per thread are loaded
 // before the first is stored.
 template <typename T>
 __device__ __forceinline__ void copy_units(const TsbRegion* __restrict__ r, uint64_t src, uint64_t dst, uint32_t ndim,
                                            uint64_t first_unit, uint64_t nunits, uint32_t units_per_run,
-                                           uint32_t tid) {
+                                           uint32_t tid, bool hint64) {
   constexpr int U = 4;
   for (uint64_t base = 0; base < nunits; base += (uint64_t)U * TSB_STRIDED_THREADS) {
     T v[U];
@@ -358,7 +376,7 @@ __device__ __forceinline__ void copy_units(const TsbRegion* __restrict__ r, uint
         }
         int64_t so, dofs;
         run_offsets(r, ndim, q, so, dofs);
-        v[i] = *(reinterpret_cast<const T*>(src + so) + k);
+        v[i] = ld_unit<T>(reinterpret_cast<const T*>(src + so) + k, hint64);
         dp[i] = reinterpret_cast<T*>(dst + dofs) + k;
       }
     }
@@ -369,7 +387,8 @@ __device__ __forceinline__ void copy_units(const TsbRegion* __restrict__ r, uint
 }
 
 __global__ void __launch_bounds__(TSB_STRIDED_THREADS)
-tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __restrict__ tiles) {
+tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __restrict__ tiles,
+                        uint32_t warp_run_min_and_flags) {
   const uint32_t tid = threadIdx.x;
   const uint4* tp = reinterpret_cast<const uint4*>(tiles + blockIdx.x);
   const uint4 t1 = __ldg(tp + 1);
@@ -389,9 +408,14 @@ tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __
   uint64_t m = src | dst | run_bytes | 16u;
   for (uint32_t d = 0; d < ndim; ++d) m |= (uint64_t)__ldg(&r->src_stride[d]) | (uint64_t)__ldg(&r->dst_stride[d]);
   const uint32_t unit = (uint32_t)(m & (~m + 1));
-  // Runs of 64 bytes or more whose addresses are NOT all 16-byte aligned go one per warp (the span copy
-  // realigns them); aligned runs and runs under 64 bytes are copied unit by unit.
-  if (run_bytes >= TSB_WARP_RUN_MIN && unit < 16u) {
+  // Runs whose addresses are NOT all 16-byte aligned go one per warp (the span copy realigns them to
+  // 16-byte stores) once they are long enough to keep a warp busy; aligned runs and shorter runs are copied
+  // unit by unit.  Measured crossover on B200 (scripts/strided_sweep.py): unit-wise copies move 0.79 / 1.45 /
+  // 2.65 / 4.0-4.4 TB/s with 1 / 2 / 4 / 8-byte units whatever the run length, one-run-per-warp moves 0.75 /
+  // 1.42 / 2.48 / 3.99 / 4.24 / 6.34 TB/s for runs of 64 / 128 / 256 / 512 / 1024 / 4096 bytes -- so the
+  // warp form wins from 128 x unit bytes on.
+  const uint32_t warp_run_min = warp_run_min_and_flags & 0x7fffffffu;
+  if (unit < 16u && run_bytes >= (uint64_t)warp_run_min * unit) {
     // the host emits whole runs per tile for this class
     const uint64_t q0 = off / run_bytes;
     const uint32_t nruns = len / (uint32_t)run_bytes;
@@ -404,14 +428,15 @@ tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __
     }
     return;
   }
+  const bool hint64 = (warp_run_min_and_flags >> 31) != 0;
   const uint32_t upr = (uint32_t)run_bytes / unit;
   const uint64_t first = off / unit;
   const uint64_t nunits = len / unit;
   switch (unit) {
-    case 1: copy_units<uint8_t>(r, src, dst, ndim, first, nunits, upr, tid); break;
-    case 2: copy_units<uint16_t>(r, src, dst, ndim, first, nunits, upr, tid); break;
-    case 4: copy_units<uint32_t>(r, src, dst, ndim, first, nunits, upr, tid); break;
-    case 8: copy_units<uint2>(r, src, dst, ndim, first, nunits, upr, tid); break;
-    default: copy_units<uint4>(r, src, dst, ndim, first, nunits, upr, tid); break;
+    case 1: copy_units<uint8_t>(r, src, dst, ndim, first, nunits, upr, tid, hint64); break;
+    case 2: copy_units<uint16_t>(r, src, dst, ndim, first, nunits, upr, tid, hint64); break;
+    case 4: copy_units<uint32_t>(r, src, dst, ndim, first, nunits, upr, tid, hint64); break;
+    case 8: copy_units<uint2>(r, src, dst, ndim, first, nunits, upr, tid, hint64); break;
+    default: copy_units<uint4>(r, src, dst, ndim, first, nunits, upr, tid, hint64); break;
   }
 }

@@ -380,6 +380,21 @@ static void flat_run(uint64_t src, uint64_t dst, uint64_t n, std::vector<TsbRun>
   *n_tiles += tsb_run_tiles(dst, n);
 }
 
+// Launch parameter of the strided kernel.  Low 31 bits: shortest run, in alignment units, that is copied
+// one-per-warp when its addresses are not 16-byte aligned (shorter ones go unit by unit); TSB200_WARP_RUN_MIN
+// overrides the default for measurements.
+static uint32_t warp_run_min() {
+  static const uint32_t v = [] {
+    const char* e = getenv("TSB200_WARP_RUN_MIN");
+    long x = e ? atol(e) : 0;
+    uint32_t r = x > 0 ? (uint32_t)x : (uint32_t)TSB_WARP_RUN_MIN;
+    const char* h = getenv("TSB200_L2_64B");  // bit 31: 64-byte L2 fetch hint on 16-byte unit loads (default on)
+    if (!(h && h[0] == '0')) r |= 0x80000000u;
+    return r;
+  }();
+  return v;
+}
+
 struct TilePlan {
   std::vector<TsbRun> flat_runs;
   uint64_t flat_tiles = 0;
@@ -764,7 +779,8 @@ static int copy_regions_impl(TsbCtx* ctx, int stream, const TsbRegion* regions, 
   }
   if (e == cudaSuccess && !plan.strided.empty()) {
     tsb_copy_strided_kernel<<<(uint32_t)plan.strided.size(), TSB_STRIDED_THREADS, 0, s>>>(
-        (const TsbRegion*)(uintptr_t)(dbuf + run_bytes + str_bytes), (const TsbTile*)(uintptr_t)(dbuf + run_bytes));
+        (const TsbRegion*)(uintptr_t)(dbuf + run_bytes + str_bytes), (const TsbTile*)(uintptr_t)(dbuf + run_bytes),
+        warp_run_min());
     e = cudaGetLastError();
   }
   if (kernel_stop && event_lookup(ctx, *kernel_stop, &ev_stop) == TSB_OK) cudaEventRecord(ev_stop, s);
@@ -988,7 +1004,7 @@ extern "C" int tsb_copy_regions_static(int device, uint64_t cuda_stream, const T
   if (e == cudaSuccess && ti) {
     tsb_copy_strided_kernel<<<(uint32_t)ti, TSB_STRIDED_THREADS, 0, s>>>(
         reinterpret_cast<const TsbRegion*>(dscratch + ri * sizeof(TsbRun) + ti * sizeof(TsbTile)),
-        reinterpret_cast<const TsbTile*>(dscratch + ri * sizeof(TsbRun)));
+        reinterpret_cast<const TsbTile*>(dscratch + ri * sizeof(TsbRun)), warp_run_min());
     e = cudaGetLastError();
   }
   if (e != cudaSuccess) return set_err(TSB_ECUDA, "tsb_copy_regions_static launch failed: %s", cudaGetErrorString(e));
