@@ -16,7 +16,7 @@ rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 
 torch.cuda.set_device(lr)
 dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
 GB = float(os.environ.get("TABLE_GB", "8"))
-cols = 128; rows = int(GB * 1e9 / 4 / cols) // (2 * world) * (2 * world)
+cols = int(os.environ.get("COLS", "128")); rows = int(GB * 1e9 / 4 / cols) // (2 * world) * (2 * world)
 
 class Sharded:  # duck-typed ShardedTensor: local shards with global offsets
     def __init__(self, boxes, fill=None):
