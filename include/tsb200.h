@@ -117,6 +117,14 @@ int tsb_ctx_counters(TsbCtx* ctx, uint64_t* kernel_launches, uint64_t* copy_call
  */
 int tsb_dev_alloc(TsbCtx* ctx, uint64_t nbytes, uint64_t* dptr);
 int tsb_dev_free(TsbCtx* ctx, uint64_t dptr);
+/*
+ * A device block that is a driver allocation of its own (not carved out of an arena segment), for
+ * blocks a peer process maps with tsb_ipc_open: mapping a peer allocation costs 10-20 ms per GB of
+ * the WHOLE allocation, so what a peer maps should hold only what that peer reads (the per-destination
+ * buffers of a reshard, reshard.py).  Freed with tsb_dev_free (an implicit device synchronisation).
+ * No counterpart in the reference, which never moves payload between ranks.
+ */
+int tsb_dev_alloc_exportable(TsbCtx* ctx, uint64_t nbytes, uint64_t* dptr);
 
 /*
  * Pinned host memory the staged buffers live in (what BufferStager.stage_buffer returns a

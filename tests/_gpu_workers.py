@@ -72,6 +72,18 @@ def p2p_reshard(rank, world, tmp):
         want = _cases.box_slice(full, (shard.metadata.shard_offsets, shard.metadata.shard_sizes)).cuda()
         assert torch.equal(shard.tensor, want)
     assert torch.equal(out_own["x"], own["x"])
+    # a reshard goes through per-destination buffers (the owner packed this rank's columns for it) ...
+    assert st.pack_launches > 0, vars(st)
+    # ... and with that turned off every destination reads the owner's whole staging block: same bytes
+    os.environ["TSB200_P2P_SCATTER"] = "0"
+    try:
+        dst1 = _sharded(1, world, shape)
+        snap.restore({"emb": StateDict(t=dst1), "own": out_own})
+        assert reshard.last_stats.pack_launches == 0 and reshard.last_stats.peer_bytes == st.peer_bytes
+        for a, b in zip(dst.local_shards(), dst1.local_shards()):
+            assert torch.equal(a.tensor, b.tensor)
+    finally:
+        del os.environ["TSB200_P2P_SCATTER"]
     # the storage-only path (reference semantics) gives the same bytes
     os.environ["TSB200_P2P_RESHARD"] = "0"
     try:

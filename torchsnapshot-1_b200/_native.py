@@ -57,6 +57,7 @@ _SIGNATURES = {
     "tsb_ctx_sm_count": (_i, [_p, ctypes.POINTER(_i)]),
     "tsb_ctx_counters": (_i, [_p, ctypes.POINTER(_u64), ctypes.POINTER(_u64), ctypes.POINTER(_u64), ctypes.POINTER(_u64)]),
     "tsb_dev_alloc": (_i, [_p, _u64, ctypes.POINTER(_u64)]),
+    "tsb_dev_alloc_exportable": (_i, [_p, _u64, ctypes.POINTER(_u64)]),
     "tsb_dev_free": (_i, [_p, _u64]),
     "tsb_host_alloc": (_i, [_p, _u64, ctypes.POINTER(_p)]),
     "tsb_host_free": (_i, [_p, _p]),
@@ -161,6 +162,12 @@ class Context:
     def dev_alloc(self, nbytes: int) -> int:
         out = _u64()
         _check(self.lib, self.lib.tsb_dev_alloc(self._h, nbytes, ctypes.byref(out)))
+        return out.value
+
+    def dev_alloc_exportable(self, nbytes: int) -> int:
+        """A device block that is its own driver allocation (what a peer maps is exactly this block)."""
+        out = _u64()
+        _check(self.lib, self.lib.tsb_dev_alloc_exportable(self._h, nbytes, ctypes.byref(out)))
         return out.value
 
     def dev_free(self, dptr: int) -> None:

@@ -286,6 +286,8 @@ struct TsbCtx {
   std::vector<uint32_t> free_events;
   std::vector<PendingScratch> pending;
   std::vector<cudaEvent_t> spare_scratch_events;
+  // device blocks that are driver allocations of their own (tsb_dev_alloc_exportable): base -> size
+  std::map<uint64_t, uint64_t> standalone;
   bool use_tma = true;  // aligned tiles through cp.async.bulk; TSB200_USE_TMA=0 turns it off
   // counters (tsb_ctx_counters)
   uint64_t n_kernel_launches = 0;  // expand + flat + strided kernels
@@ -519,6 +521,8 @@ int tsb_ctx_destroy(TsbCtx* ctx) {
   for (auto e : ctx->events) cudaEventDestroy(e);
   for (auto e : ctx->spare_scratch_events) cudaEventDestroy(e);
   for (int i = 0; i < TSB_NUM_STREAMS; ++i) cudaStreamDestroy(ctx->streams[i]);
+  for (auto& kv : ctx->standalone) cudaFree((void*)(uintptr_t)kv.first);
+  ctx->standalone.clear();
   ctx->host_arena->destroy();
   ctx->dev_arena->destroy();
   ctx->scratch_host->destroy();
@@ -566,8 +570,39 @@ int tsb_dev_alloc(TsbCtx* ctx, uint64_t nbytes, uint64_t* dptr) {
   return rc;
 }
 
+int tsb_dev_alloc_exportable(TsbCtx* ctx, uint64_t nbytes, uint64_t* dptr) {
+  CHECK_CTX(ctx);
+  if (!dptr) return set_err(TSB_EINVAL, "null argument");
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, nbytes ? nbytes : 1);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    // give cached staging segments back and try once more before reporting the shortage
+    ctx->dev_arena->trim();
+    e = cudaMalloc(&p, nbytes ? nbytes : 1);
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      return set_err(TSB_EAGAIN, "exportable device block of %llu bytes: %s", (unsigned long long)nbytes,
+                     cudaGetErrorString(e));
+    }
+  }
+  std::lock_guard<std::mutex> g(ctx->mu);
+  ctx->standalone[(uint64_t)(uintptr_t)p] = nbytes;
+  *dptr = (uint64_t)(uintptr_t)p;
+  return TSB_OK;
+}
+
 int tsb_dev_free(TsbCtx* ctx, uint64_t dptr) {
   CHECK_CTX(ctx);
+  {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    auto it = ctx->standalone.find(dptr);
+    if (it != ctx->standalone.end()) {
+      ctx->standalone.erase(it);
+      CUDA_TRY(cudaFree((void*)(uintptr_t)dptr));
+      return TSB_OK;
+    }
+  }
   return ctx->dev_arena->free(dptr);
 }
 
@@ -1123,7 +1158,20 @@ int tsb_ipc_export(TsbCtx* ctx, uint64_t dptr, uint8_t* handle, uint64_t* offset
   if (!handle || !offset) return set_err(TSB_EINVAL, "null argument");
   static_assert(sizeof(cudaIpcMemHandle_t) == TSB_IPC_HANDLE_BYTES, "ipc handle size");
   uint64_t base = 0, size = 0;
-  if (!ctx->dev_arena->find_segment(dptr, &base, &size))
+  bool found = false;
+  {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    auto it = ctx->standalone.upper_bound(dptr);
+    if (it != ctx->standalone.begin()) {
+      --it;
+      if (dptr < it->first + std::max<uint64_t>(it->second, 1)) {
+        base = it->first;
+        size = it->second;
+        found = true;
+      }
+    }
+  }
+  if (!found && !ctx->dev_arena->find_segment(dptr, &base, &size))
     return set_err(TSB_EINVAL, "ipc_export: 0x%llx is not device-arena memory", (unsigned long long)dptr);
   cudaIpcMemHandle_t h;
   CUDA_TRY(cudaIpcGetMemHandle(&h, (void*)(uintptr_t)base));

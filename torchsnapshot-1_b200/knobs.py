@@ -53,6 +53,13 @@ def is_p2p_reshard_enabled() -> bool:
     return os.getenv("TSB200_P2P_RESHARD", "1").lower() not in ("0", "false")
 
 
+def is_p2p_scatter_enabled() -> bool:
+    """Reshards (units whose bytes are partitioned among the ranks): the owner packs one buffer per
+    destination rank and the destination maps only that buffer (reshard.py); TSB200_P2P_SCATTER=0 makes every
+    destination map the owner's whole staging block instead (the replicated-state scheme)."""
+    return os.getenv("TSB200_P2P_SCATTER", "1").lower() not in ("0", "false")
+
+
 def trim_arenas_after_use() -> bool:
     """TSB200_TRIM_ARENAS=1: give the device staging and pinned host segments back to the driver when a
     take / restore has drained (a trainer short of HBM wants its memory back; the next take then pays for

@@ -13,7 +13,17 @@ and sent over PCIe up to world-size times.  Here
      own staging blocks or, through CUDA IPC mappings, the staging blocks of its peers -- strided
      boxes read directly over NVLink / NVSwitch by the same kernel that packs and unpacks slabs.
 
-Only metadata crosses the process group (two object all-gathers and two barriers); the payload moves
+Two kinds of unit are told apart from the gathered needs (`scatter_keys`).  Replicated state -- every rank
+needs the whole unit -- is read by every destination straight out of the owner's staging block.  A reshard
+-- the needs of the ranks add up to one copy of the unit -- goes through per-destination buffers: the
+destinations tell the owner which strided boxes of the unit they want (`Request`, one more object
+all-gather), the owner packs, as soon as the unit is resident, each destination's boxes back to back into a
+buffer of that destination's own, and the destination maps only that buffer and reads it with contiguous
+loads.  That is what keeps the CUDA IPC mapping cost (10-20 ms per GB of the mapped ALLOCATION) proportional
+to what a rank receives instead of to what its peers hold, and turns 64-byte strided reads over NVLink into
+flat ones.
+
+Only metadata crosses the process group (object all-gathers and barriers); the payload moves
 over storage -> PCIe once and then over NVLink.  The result is bit-identical to the storage-only path
 (tests/test_gpu_multi.py checks both against each other and against the source data).
 """
@@ -27,6 +37,7 @@ from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
 
 import torch
 
+from . import knobs
 from ._native import STREAM_H2D, STREAM_PACK
 from .engine import get_engine
 from .io_preparer import ShardedTensorIOPreparer, overlap_wrt_saved
@@ -132,7 +143,8 @@ class ReshardStats:
         self.local_bytes = 0  # bytes copied from this rank's own staging
         self.peer_bytes = 0  # bytes this rank pulled over NVLink
         self.copy_ms = 0.0  # device time of the copy kernels (CUDA events)
-        self.launches = 0
+        self.launches = 0  # launches that fill this rank's tensors (one per call)
+        self.pack_launches = 0  # owner side: units split into per-destination buffers (one per owned unit)
         self.skipped: List[str] = []  # sharded paths some rank did not offer: load them the ordinary way
         self.phase_ms: Dict[str, float] = {}  # wall-clock phases: plan, read, exchange, copy, barrier
 
@@ -171,6 +183,52 @@ def plan_unit_owners(needs_by_rank: Sequence[Dict[UnitKey, Tuple[int, int]]]) ->
         load[owner] += nbytes
         owners[key] = owner
     return owners
+
+
+# A request: what one rank wants out of one unit, as strided boxes relative to the unit's first byte --
+# (source offset, run bytes, outer sizes, source byte strides).  The destination half of the same region
+# (address and strides in the requesting rank's memory) never leaves that rank.
+Request = Tuple[int, int, Tuple[int, ...], Tuple[int, ...]]
+_PACK_ALIGN = 512  # start of every packed box inside a per-destination buffer
+
+
+def scatter_keys(needs_by_rank: Sequence[Dict[UnitKey, Tuple[int, int]]]) -> List[UnitKey]:
+    """Units whose bytes are PARTITIONED among the ranks (the needs add up to about one copy of the unit: a
+    reshard), as opposed to replicated state every rank needs whole.  Their owner packs, per destination
+    rank, exactly the bytes that rank asked for into a buffer of its own; the destination then maps and
+    reads only that buffer.  Deterministic from the gathered needs."""
+    total: Dict[UnitKey, int] = {}
+    size: Dict[UnitKey, int] = {}
+    for d in needs_by_rank:
+        for key, (need, nbytes) in d.items():
+            total[key] = total.get(key, 0) + need
+            size[key] = max(size.get(key, 0), nbytes)
+    return sorted(k for k in total if total[k] * 4 <= size[k] * 5)
+
+
+def packed_strides(run_bytes: int, sizes: Sequence[int]) -> Tuple[int, ...]:
+    """Byte strides of the outer dims when the runs of a box are laid out back to back."""
+    out = [0] * len(sizes)
+    acc = run_bytes
+    for i in range(len(sizes) - 1, -1, -1):
+        out[i] = acc
+        acc *= int(sizes[i])
+    return tuple(out)
+
+
+def packed_layout(requests: Dict[UnitKey, List[Request]]) -> Tuple[Dict[Tuple[UnitKey, int], int], int]:
+    """Where each requested box starts inside the per-destination buffer, and the buffer's size.  The owner
+    and the destination both call this on the same request table, so no offsets are exchanged."""
+    offsets: Dict[Tuple[UnitKey, int], int] = {}
+    cursor = 0
+    for key in sorted(requests):
+        for i, (_src_off, run_bytes, sizes, _strides) in enumerate(requests[key]):
+            offsets[(key, i)] = cursor
+            n = run_bytes
+            for s in sizes:
+                n *= int(s)
+            cursor += (n + _PACK_ALIGN - 1) // _PACK_ALIGN * _PACK_ALIGN
+    return offsets, cursor
 
 
 def sharded_units(items: Sequence[Tuple[str, ShardedTensorEntry, Any]]) -> List[Unit]:
@@ -255,6 +313,20 @@ def p2p_restore_units(
     staged: Dict[UnitKey, int] = {}
     blocks: List[int] = []  # device arena blocks to free at the end
     opened: Dict[Tuple[int, bytes], int] = {}
+    # ---- partitioned units (a reshard): the owner packs per destination, see scatter_keys() ----------
+    scatter = set(scatter_keys(gathered)) if knobs.is_p2p_scatter_enabled() else set()
+    my_regions: Dict[UnitKey, List[RegionTuple]] = {}  # regions of the scatter units I pull, source relative to the unit
+    wanted_from: Dict[int, Dict[UnitKey, List[Request]]] = {}
+    for key, unit in mine_by_key.items():
+        if key in scatter and owners.get(key) not in (None, rank) and unit.need:
+            regs = unit.regions(0)
+            my_regions[key] = regs
+            wanted_from.setdefault(owners[key], {})[key] = [(r[0], r[2], tuple(r[3]), tuple(r[4])) for r in regs]
+    all_wanted: List[Any] = [None] * world
+    if scatter:
+        pg.all_gather_object(all_wanted, wanted_from)
+    pack_by_key: Dict[UnitKey, List[RegionTuple]] = {}  # owner side: unit -> boxes to pack once it is resident
+    peer_buffers: Dict[int, int] = {}  # destination rank -> its packed buffer on this rank
     executor = ThreadPoolExecutor(max_workers=4, thread_name_prefix="tsb-reshard")
     ipc_executor = ThreadPoolExecutor(max_workers=8, thread_name_prefix="tsb-ipc")
     try:
@@ -278,8 +350,30 @@ def p2p_restore_units(
                         blocks.append(staged[k])
                 except Exception as e:  # noqa: BLE001 - told to every rank right below
                     staging_error = f"rank {rank}: no device staging for {total_owned} bytes ({e})"
+        # ---- per-destination buffers for the partitioned units this rank owns ---------------------
+        if scatter and staging_error is None:
+            try:
+                for peer in range(world):
+                    asked = (all_wanted[peer] or {}).get(rank) if peer != rank else None
+                    if not asked:
+                        continue
+                    offsets, total = packed_layout(asked)
+                    buf = ctx.dev_alloc_exportable(total)
+                    blocks.append(buf)
+                    peer_buffers[peer] = buf
+                    for key, reqs in asked.items():
+                        for i, (src_off, run_bytes, bsizes, sstrides) in enumerate(reqs):
+                            pack_by_key.setdefault(key, []).append(
+                                (staged[key] + src_off, buf + offsets[(key, i)], run_bytes, tuple(bsizes),
+                                 tuple(sstrides), packed_strides(run_bytes, bsizes))
+                            )
+            except Exception as e:  # noqa: BLE001 - told to every rank right below
+                staging_error = f"rank {rank}: no per-destination staging ({e})"
         # ---- addresses are known before any byte is read: publish them now (IPC handle + offset) ---
-        exports: Any = staging_error or {k: ctx.ipc_export(dptr) for k, dptr in staged.items()}
+        exports: Any = staging_error or {
+            "shared": {k: ctx.ipc_export(dptr) for k, dptr in staged.items() if k not in scatter},
+            "scatter": {peer: ctx.ipc_export(buf) for peer, buf in peer_buffers.items()},
+        }
         all_exports: List[Any] = [None] * world
         pg.all_gather_object(all_exports, exports)
         errors = [x for x in all_exports if isinstance(x, str)]
@@ -298,26 +392,37 @@ def p2p_restore_units(
             loop = asyncio.get_running_loop()
             # mapping a peer's staging block costs milliseconds per GiB: do it on worker threads, all peers
             # at once, while the event loop keeps the storage reads and H2D copies going
-            wanted = {(owners[key], all_exports[owners[key]][key][0]) for key, unit in mine_by_key.items()
-                      if owners.get(key) is not None and owners[key] != rank and unit.need}
+            wanted = {(owners[key], all_exports[owners[key]]["shared"][key][0]) for key, unit in mine_by_key.items()
+                      if owners.get(key) is not None and owners[key] != rank and unit.need and key not in scatter}
+            wanted |= {(owner, all_exports[owner]["scatter"][rank][0]) for owner in wanted_from}
             if wanted:
                 await asyncio.gather(*(loop.run_in_executor(ipc_executor, open_peer, hk) for hk in sorted(wanted)))
             n = 0
             for key, unit in mine_by_key.items():
                 owner = owners.get(key)
-                if owner is None or unit.need == 0:
+                if owner is None or unit.need == 0 or key in my_regions:
                     continue
                 if owner == rank:
                     src_base = staged[key]
                     stats.local_bytes += unit.need
                 else:
-                    handle, offset = all_exports[owner][key]
+                    handle, offset = all_exports[owner]["shared"][key]
                     src_base = opened[(owner, handle)] + offset
                     stats.peer_bytes += unit.need
                 regions.extend(unit.regions(src_base))
                 n += 1
                 if n % 8 == 0:
                     await asyncio.sleep(0)  # let the read pipeline dispatch
+            # partitioned units owned by a peer: my boxes lie back to back in that peer's buffer for me
+            for owner, asked in wanted_from.items():
+                handle, offset = all_exports[owner]["scatter"][rank]
+                base = opened[(owner, handle)] + offset
+                offsets, _total = packed_layout(asked)
+                for key in asked:
+                    for i, r in enumerate(my_regions[key]):
+                        regions.append((base + offsets[(key, i)], r[1], r[2], tuple(r[3]),
+                                        packed_strides(r[2], r[3]), tuple(r[5])))
+                    stats.peer_bytes += mine_by_key[key].need
 
         async def read_all() -> None:
             loop = asyncio.get_running_loop()
@@ -340,6 +445,11 @@ def p2p_restore_units(
                         held = False
                         ctx.memcpy_h2d(STREAM_H2D, staged[key], pbuf.ptr, nbytes)
                         ev = ctx.event_record(STREAM_H2D)
+                        packs = pack_by_key.get(key)
+                        if packs:  # resident now: split it into the per-destination buffers (device side, async)
+                            ctx.stream_wait_event(STREAM_PACK, ev)
+                            eng.copy_region_array(regions_to_array(packs), STREAM_PACK)
+                            stats.pack_launches += 1
                         try:
                             await loop.run_in_executor(executor, ctx.event_sync, ev)
                         finally:
@@ -358,6 +468,8 @@ def p2p_restore_units(
         failure: Optional[str] = None
         try:
             event_loop.run_until_complete(read_all())
+            if pack_by_key:
+                ctx.stream_sync(STREAM_PACK)  # the per-destination buffers are complete before anybody is told so
         except Exception as e:  # noqa: BLE001 - reported to every rank below
             failure = f"rank {rank}: {type(e).__name__}: {e}"
         t_bar = time.monotonic()
@@ -391,6 +503,13 @@ def p2p_restore_units(
         for base_addr in opened.values():
             try:
                 ctx.ipc_close(base_addr)
+            except Exception:  # pragma: no cover
+                pass
+        if scatter:
+            # per-destination buffers are driver allocations that are freed for good below: every peer has to
+            # have dropped its mapping first (every rank sees the same `scatter`, so every rank is here)
+            try:
+                pg.barrier()
             except Exception:  # pragma: no cover
                 pass
         for dptr in blocks:
