@@ -43,7 +43,7 @@ def run(name, boxes, p2p):
     os.environ["TSB200_P2P_RESHARD"] = "1" if p2p else "0"
     dst = Sharded(boxes)
     best = None
-    for it in range(3):
+    for it in range(3 if p2p else int(os.environ.get("STORAGE_ONLY_ITERS", "3"))):
         sync(); t0 = time.monotonic()
         snap.restore({"emb": StateDict(t=dst)})
         sync(); dt = time.monotonic() - t0
