@@ -8,7 +8,7 @@ here because the manifest format needs it, not because it is on the hot path."""
 from collections import OrderedDict
 from typing import Any, Dict, Tuple
 
-from .manifest import DictEntry, Entry, ListEntry, Manifest, OrderedDictEntry
+from .manifest import DictEntry, ListEntry, Manifest, OrderedDictEntry
 
 
 def _encode(s: str) -> str:

@@ -18,7 +18,6 @@ import itertools
 import logging
 import math
 import os
-import warnings
 from collections import defaultdict
 from concurrent.futures import Executor
 from dataclasses import dataclass
@@ -50,7 +49,6 @@ from .serialization import (
     SUPPORTED_QUANTIZED_DTYPES,
     dtype_to_element_size,
     dtype_to_string,
-    is_buffer_protocol_dtype,
     string_to_dtype,
 )
 

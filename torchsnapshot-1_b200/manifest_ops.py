@@ -12,7 +12,6 @@ from collections import defaultdict
 from typing import Any, Dict, List, Tuple
 
 from .manifest import (
-    Entry,
     is_container_entry,
     is_dict_entry,
     is_replicated,
