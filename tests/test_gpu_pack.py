@@ -434,3 +434,32 @@ def test_random_views_one_launch_fuzz(engine, seed):
     _launch(engine, back)
     for i, (tg, tc) in enumerate(zip(twins_g, twins_c)):
         assert _to_host(tg.reshape(-1).view(torch.uint8)) == tc.reshape(-1).view(torch.uint8).numpy().tobytes(), i
+
+
+def test_exportable_block_is_its_own_allocation(engine):
+    """tsb_dev_alloc_exportable: a block a peer can map on its own (offset 0 of its own IPC handle, unlike
+    arena blocks, which export their whole segment), usable as a copy target, freed through tsb_dev_free."""
+    ctx = engine.ctx
+    n = (3 << 20) + 123
+    block = ctx.dev_alloc_exportable(n)
+    arena_a = ctx.dev_alloc(1 << 20)
+    arena_b = ctx.dev_alloc(1 << 20)
+    try:
+        handle, offset = ctx.ipc_export(block)
+        assert offset == 0 and len(handle) == 64
+        _h2, inner = ctx.ipc_export(block + 4096)
+        assert inner == 4096 and _h2 == handle
+        ha, off_a = ctx.ipc_export(arena_a)
+        hb, off_b = ctx.ipc_export(arena_b)
+        assert ha == hb and off_a != off_b and ha != handle  # arena blocks share their segment's handle
+        src = torch.arange(n, dtype=torch.int64, device="cuda").to(torch.uint8)
+        _launch(engine, [(src.data_ptr(), block, n, (), (), ())])
+        back = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        _launch(engine, [(block, back.data_ptr(), n, (), (), ())])
+        assert torch.equal(back, src)
+    finally:
+        ctx.dev_free(block)
+        ctx.dev_free(arena_a)
+        ctx.dev_free(arena_b)
+    with pytest.raises(_native.TsbError):
+        ctx.dev_free(block)
