@@ -330,19 +330,30 @@ def p2p_restore_units(
     executor = ThreadPoolExecutor(max_workers=4, thread_name_prefix="tsb-reshard")
     ipc_executor = ThreadPoolExecutor(max_workers=8, thread_name_prefix="tsb-ipc")
     try:
-        # ---- staging for the units this rank owns: ONE block when the arena allows it, so that every
-        # peer maps a single IPC handle (cudaIpcOpenMemHandle costs milliseconds per handle) ----------
+        # ---- staging for the units this rank owns.  Units that peers read whole (replicated state) share
+        # ONE block that is a driver allocation of its own: every peer maps a single IPC handle, and what it
+        # maps is exactly that block, whatever the arena's segments look like after earlier takes (mapping
+        # costs 10-20 ms per GB of the allocation).  Units that are packed per destination stay private, in
+        # the arena. -------------------------------------------------------------------------------------
         total_owned = sum((sizes[k] + 511) // 512 * 512 for k in owned)
         staging_error: Optional[str] = None
         if owned:
             try:
-                base = ctx.dev_alloc(total_owned)
-                blocks.append(base)
-                off = 0
-                for k in owned:
-                    staged[k] = base + off
-                    off += (sizes[k] + 511) // 512 * 512
-            except Exception:  # larger than one arena segment can be: one block per unit
+                for exported, keys in ((True, [k for k in owned if k not in scatter]),
+                                       (False, [k for k in owned if k in scatter])):
+                    if not keys:
+                        continue
+                    nbytes = sum((sizes[k] + 511) // 512 * 512 for k in keys)
+                    base = ctx.dev_alloc_exportable(nbytes) if exported and world > 1 else ctx.dev_alloc(nbytes)
+                    blocks.append(base)
+                    off = 0
+                    for k in keys:
+                        staged[k] = base + off
+                        off += (sizes[k] + 511) // 512 * 512
+            except Exception:  # no room for one block of that size: one arena block per unit
+                for b in blocks:
+                    ctx.dev_free(b)
+                blocks.clear()
                 staged.clear()
                 try:
                     for k in owned:
@@ -505,9 +516,9 @@ def p2p_restore_units(
                 ctx.ipc_close(base_addr)
             except Exception:  # pragma: no cover
                 pass
-        if scatter:
-            # per-destination buffers are driver allocations that are freed for good below: every peer has to
-            # have dropped its mapping first (every rank sees the same `scatter`, so every rank is here)
+        if world > 1:
+            # exported blocks are driver allocations that are freed for good below: every peer has to have
+            # dropped its mapping first (every rank that got this far has units, so every rank is here)
             try:
                 pg.barrier()
             except Exception:  # pragma: no cover
