@@ -168,3 +168,43 @@ def elastic_restore(rank, world, tmp):
         o, n = shard.metadata.shard_offsets[0], shard.metadata.shard_sizes[0]
         assert torch.equal(shard.tensor, full[o : o + n]), (rank, o, n)
     assert torch.equal(rep["w"], _cases.raw_tensor(901, [33, 7], torch.float32)) and rep["step"] == 5
+
+
+def object_collectives(rank, world, tmp):
+    """PGWrapper.scatter_object_list (reference pg_wrapper.py:58-89) and the collective form of the
+    replicated-entry consolidation (partitioner.py:306-316) over a real 2-rank group."""
+    from torchsnapshot_b200.manifest import ChunkedTensorEntry, Shard, TensorEntry
+    from torchsnapshot_b200.partitioner import consolidate_replicated_entries_dist
+    from torchsnapshot_b200.pg_wrapper import PGWrapper
+
+    pg = PGWrapper()
+    out = [None]
+    pg.scatter_object_list(out, [{"for": r, "payload": list(range(r + 3))} for r in range(world)] if rank == 0 else None)
+    assert out[0] == {"for": rank, "payload": list(range(rank + 3))}
+    if rank == 0:
+        try:
+            pg.scatter_object_list([None], [1])  # wrong length on the source rank
+        except RuntimeError:
+            pass
+        else:
+            raise AssertionError("a short input_list must be refused")
+
+    def chunk(i):
+        t = TensorEntry(location=f"replicated/w_{i}_0", serializer="buffer_protocol", dtype="torch.float32",
+                        shape=[2, 4], replicated=False)
+        return Shard(offsets=[2 * i, 0], sizes=[2, 4], tensor=t)
+
+    # each rank wrote one chunk of a replicated chunked tensor, plus a private entry of its own
+    mine = {
+        "m/w": ChunkedTensorEntry(dtype="torch.float32", shape=[4, 4], chunks=[chunk(rank)], replicated=True),
+        f"m/private_{rank}": TensorEntry(location=f"{rank}/m/private", serializer="buffer_protocol",
+                                         dtype="torch.int64", shape=[3], replicated=False),
+    }
+    merged = consolidate_replicated_entries_dist(mine, pg)
+    assert f"m/private_{rank}" in merged and f"m/private_{1 - rank}" not in merged
+    if rank == 0:  # replicated entries are listed once, under rank 0, with every rank's chunks in offset order
+        assert [c.offsets for c in merged["m/w"].chunks] == [[0, 0], [2, 0]]
+    else:
+        assert "m/w" not in merged
+    keep_all = consolidate_replicated_entries_dist(mine, pg, dedup=False)
+    assert [c.offsets for c in keep_all["m/w"].chunks] == [[0, 0], [2, 0]]

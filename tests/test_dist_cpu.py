@@ -50,6 +50,11 @@ def test_async_take_commit_across_ranks(tmp_path):
     _launch("async_commit", tmp_path)
 
 
+@pytest.mark.timeout(300)
+def test_object_collectives_of_the_host_mirror(tmp_path):
+    _launch("object_collectives", tmp_path)
+
+
 @pytest.mark.timeout(600)
 @pytest.mark.parametrize("new_world", [1, 3])
 def test_elastic_restore_at_another_world_size(tmp_path, new_world):
