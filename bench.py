@@ -303,7 +303,7 @@ def main():
         return st.device_ms(), st.kernel_ms(), st.kernel_bytes(), st.bytes
 
     res = {"dev_ms": [], "kern_ms": [], "kern_bytes": [], "take_wall": [], "restore_wall": [], "blocked_ms": [],
-           "unpack_ms": [], "step_wall": []}
+           "unpack_ms": [], "step_wall": [], "restore_phases": []}
     counters0 = None
     clocks = ClockSampler(local_rank)
     with clocks:
@@ -335,7 +335,9 @@ def main():
             unpack_ms = scheduler.last_read_stats.unpack_ms if scheduler.last_read_stats else 0.0
             restore_h2d = scheduler.last_read_stats.device_bytes if scheduler.last_read_stats else 0
             restore_peer = 0
+            restore_phases = None
             if reshard.last_stats is not None:  # N > 1: shared read + NVLink fan-out of the replicated state
+                restore_phases = {k: round(v, 1) for k, v in reshard.last_stats.phase_ms.items()}
                 unpack_ms += reshard.last_stats.copy_ms
                 restore_h2d += reshard.last_stats.read_bytes
                 restore_peer = reshard.last_stats.peer_bytes
@@ -360,6 +362,7 @@ def main():
                 res["restore_wall"].append(max_over_ranks(restore_wall))
                 res["blocked_ms"].append(max_over_ranks(blocked))
                 res["unpack_ms"].append(unpack_ms)
+                res["restore_phases"].append(restore_phases)
                 res["step_wall"].append(max_over_ranks(time.monotonic() - s0))
     counters1 = eng.ctx.counters()
     # verify once, outside the timed region, that the restored bytes are the saved bytes
@@ -439,7 +442,9 @@ def main():
                         "note": ("Snapshot.restore from tmpfs into CUDA tensors on every rank, wall clock; N > 1: each "
                                  "replicated byte is read from storage by one rank and fans out over NVLink"),
                         "unpack_kernel_ms": round(sum(res["unpack_ms"]) / K, 3),
-                        "h2d_bytes_per_step": int(restore_h2d), "nvlink_bytes_per_rank": int(restore_peer)},
+                        "h2d_bytes_per_step": int(restore_h2d), "nvlink_bytes_per_rank": int(restore_peer),
+                        "ms_per_step": [round(1e3 * x, 1) for x in res["restore_wall"]],
+                        "rank0_p2p_phases_ms_per_step": res["restore_phases"]},
             "async_take_blocked_ms": round(sum(res["blocked_ms"]) / K, 2),
             "wall_ms_per_step": round(1e3 * sum(res["step_wall"]) / K, 1),
             "gpu_launches": int(total_launches),

@@ -509,6 +509,7 @@ def p2p_restore_units(
         pg.barrier()  # nobody may free its staging while a peer still reads it
         stats.phase_ms["barrier"] = 1e3 * (time.monotonic() - t_end)
     finally:
+        t_cleanup = time.monotonic()
         executor.shutdown(wait=False)
         ipc_executor.shutdown(wait=True)
         for base_addr in opened.values():
@@ -525,6 +526,7 @@ def p2p_restore_units(
                 pass
         for dptr in blocks:
             ctx.dev_free(dptr)
+        stats.phase_ms["cleanup"] = 1e3 * (time.monotonic() - t_cleanup)  # unmap peers, barrier, free exported blocks
     return stats
 
 
