@@ -177,3 +177,32 @@ def box_slice(t: torch.Tensor, box: Box) -> torch.Tensor:
     for d, (o, s) in enumerate(zip(off, sizes)):
         t = t.narrow(d, o, s)
     return t
+
+
+def random_view(rs, base: torch.Tensor) -> torch.Tensor:
+    """A random non-overlapping view of `base`: per-dim slices with steps, then a random permutation, then
+    (sometimes) a dropped leading index -- the shapes torch hands a stager in practice, and then some."""
+    idx = []
+    for n in base.shape:
+        lo = int(rs.randint(0, max(n // 3, 1)))
+        hi = int(rs.randint(lo + 1, n + 1))
+        step = int(rs.choice([1, 1, 1, 2, 3]))
+        idx.append(slice(lo, hi, step))
+    v = base[tuple(idx)]
+    if v.ndim > 1 and rs.rand() < 0.6:
+        v = v.permute(*[int(i) for i in rs.permutation(v.ndim)])
+    if v.ndim > 1 and rs.rand() < 0.2:
+        v = v[int(rs.randint(0, v.shape[0]))]
+    return v
+
+
+def random_base_shape(rs, rank: int, max_log2_elems: float) -> List[int]:
+    """A random shape of `rank` dims with about 2^U(4, max_log2_elems) elements."""
+    budget = int(2 ** rs.uniform(4, max_log2_elems))
+    shape = []
+    for d in range(rank):
+        n = max(1, int(round(budget ** (1.0 / (rank - d)) * rs.uniform(0.5, 1.5)))) if budget > 1 else 1
+        n = min(n, budget)
+        shape.append(n)
+        budget = max(budget // n, 1)
+    return shape

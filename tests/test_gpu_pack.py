@@ -357,23 +357,6 @@ def test_regions_beyond_4GiB(engine):
     assert int(back.view(rows, pitch)[:, :8].sum()) == 0 and int(back.view(rows, pitch)[:, 8 + run :].sum()) == 0
 
 
-def _random_view(rs, base: torch.Tensor) -> torch.Tensor:
-    """A random non-overlapping view of `base`: per-dim slices with steps, then a random permutation, then
-    (sometimes) a dropped leading index -- the shapes torch hands a stager in practice, and then some."""
-    idx = []
-    for n in base.shape:
-        lo = int(rs.randint(0, max(n // 3, 1)))
-        hi = int(rs.randint(lo + 1, n + 1))
-        step = int(rs.choice([1, 1, 1, 2, 3]))
-        idx.append(slice(lo, hi, step))
-    v = base[tuple(idx)]
-    if v.ndim > 1 and rs.rand() < 0.6:
-        v = v.permute(*[int(i) for i in rs.permutation(v.ndim)])
-    if v.ndim > 1 and rs.rand() < 0.2:
-        v = v[int(rs.randint(0, v.shape[0]))]
-    return v
-
-
 @pytest.mark.parametrize("seed", [0, 1, 2, 3])
 def test_random_views_one_launch_fuzz(engine, seed):
     """~150 random strided views of every buffer-protocol dtype, ranks 0-5, packed back to back at arbitrary
@@ -401,9 +384,9 @@ def test_random_views_one_launch_fuzz(engine, seed):
             gpu_views.append(gbase)
             continue
         state = rs.get_state()
-        cpu_views.append(_random_view(rs, base))
+        cpu_views.append(_cases.random_view(rs, base))
         rs.set_state(state)
-        gpu_views.append(_random_view(rs, gbase))
+        gpu_views.append(_cases.random_view(rs, gbase))
     # slab layout: members back to back with small random gaps, so offsets have every alignment
     offs, total = [], 3
     for v in cpu_views:

@@ -104,3 +104,40 @@ def test_region_array_layout():
 def test_contiguous_strides():
     assert contiguous_strides([2, 3, 4], 2) == [24, 8, 2]
     assert contiguous_strides([], 4) == []
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_random_views_fuzz_on_host(seed):
+    """The CPU twin of tests/test_gpu_pack.py::test_random_views_one_launch_fuzz: ~200 random strided views
+    (ranks 0-5, every buffer-protocol dtype, slices with steps, permutations) -> regions -> memmove
+    interpreter, compared with the oracle's serialisation, both directions."""
+    rs = np.random.RandomState(500 + seed)
+    dtypes = list(_cases.DTYPES.values())
+    for i in range(200):
+        rank = int(rs.randint(0, 6))
+        shape = _cases.random_base_shape(rs, rank, 13)
+        dtype = dtypes[int(rs.randint(0, len(dtypes)))]
+        base = _cases.raw_tensor(seed * 1000 + i, shape, dtype)
+        state = rs.get_state()
+        view = _cases.random_view(rs, base) if rank else base
+        n = view.numel() * view.element_size()
+        off = int(rs.randint(0, 16))
+        buf = np.full(n + 32, 0x3C, dtype=np.uint8)
+        regions = pack_regions(view, buf.ctypes.data + off)
+        assert regions_payload_bytes(regions) == n and all(len(r[3]) <= TSB_MAX_DIMS for r in regions)
+        _sim.run_regions(regions)
+        want = oracle.serialize(view)
+        assert buf[off : off + n].tobytes() == want, (i, shape, view.shape, view.stride())
+        assert buf[:off].tobytes() == b"\x3c" * off and buf[off + n :].tobytes() == b"\x3c" * (32 - off)
+        # scatter back into a marker-filled twin with the same geometry; bytes outside the view stay markers
+        nbytes = base.numel() * base.element_size()
+        twin = torch.full((nbytes,), 0xA7, dtype=torch.uint8).view(dtype).reshape(base.shape)
+        ref = torch.full((nbytes,), 0xA7, dtype=torch.uint8).view(dtype).reshape(base.shape)
+        rs2 = np.random.RandomState(0)
+        rs2.set_state(state)
+        tv = _cases.random_view(rs2, twin) if rank else twin
+        rs2.set_state(state)
+        rv = _cases.random_view(rs2, ref) if rank else ref
+        _sim.run_regions(unpack_regions(buf.ctypes.data + off, tv))
+        oracle.deserialize_into(rv, want)
+        assert twin.reshape(-1).view(torch.uint8).numpy().tobytes() == ref.reshape(-1).view(torch.uint8).numpy().tobytes(), i
