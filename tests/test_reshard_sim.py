@@ -1,0 +1,207 @@
+"""The peer-to-peer restore orchestration of reshard.py, end to end on the CPU (tests/_p2p_sim.py): ranks are
+threads, device memory is host memory, the copy kernel is the memmove interpreter.  What is checked here is
+everything around the CUDA calls -- who owns which unit, what each destination asks for, where the owner
+packs it, which regions each rank launches, that replicated units are shared whole while reshards go through
+per-destination buffers, and that every rank ends up with the bytes the saved tensor holds.  The same flows
+run on real GPUs in tests/test_gpu_multi.py."""
+
+import asyncio
+import threading
+from types import SimpleNamespace as NS
+
+import pytest
+import torch
+
+import _cases
+import _p2p_sim
+from torchsnapshot_b200 import knobs, reshard
+from torchsnapshot_b200.batcher import batch_read_requests
+from torchsnapshot_b200.io_preparer import prepare_read
+from torchsnapshot_b200.manifest_ops import get_manifest_for_rank
+from torchsnapshot_b200.snapshot import Snapshot, StateDict
+from torchsnapshot_b200.storage_plugins.fs import FSStoragePlugin
+
+ROWS, COLS = 96, 40
+
+
+class Sharded:
+    """Duck-typed ShardedTensor over CPU tensors: local shards with global offsets."""
+
+    def __init__(self, boxes, full=None):
+        self._shards = []
+        for off, sizes in boxes:
+            t = _cases.box_slice(full, (off, sizes)).contiguous() if full is not None else torch.zeros(sizes)
+            self._shards.append(NS(tensor=t, metadata=NS(shard_offsets=list(off), shard_sizes=list(sizes))))
+
+    def local_shards(self):
+        return self._shards
+
+    def metadata(self):
+        return NS(size=[ROWS, COLS])
+
+    def sharding_spec(self):
+        return None
+
+
+@pytest.fixture
+def sharded_duck(monkeypatch):
+    import torchsnapshot_b200.io_preparer as iop
+    import torchsnapshot_b200.snapshot as snapmod
+
+    monkeypatch.setattr(iop, "_is_sharded_tensor", lambda o: isinstance(o, Sharded))
+    monkeypatch.setattr(snapmod, "_is_sharded_tensor", lambda o: isinstance(o, Sharded))
+
+
+def _take(tmp_path, full, replicated_extra):
+    """A snapshot of a [ROWS, COLS] fp32 table saved row-wise by "4 ranks" (four local shards of one process,
+    each subdivided into pieces of 8 rows) plus a few dense tensors that play the replicated state."""
+    per = ROWS // 4
+    src = Sharded([([r * per, 0], [per, COLS]) for r in range(4)], full)
+    with knobs.override_max_shard_size_bytes(8 * COLS * 4):
+        snap = Snapshot.take(str(tmp_path / "snap"), {"emb": StateDict(t=src), "rep": StateDict(**replicated_extra)})
+    return snap
+
+
+def _run_ranks(world, root, units_of, monkeypatch, storage_of=None, expect_errors=False):
+    """Run reshard.p2p_restore_units on `world` threads; returns (stats per rank, call log, engines) -- or,
+    with expect_errors, the (rank, exception) pairs."""
+    registry, log = {}, []
+    engines = [_p2p_sim.FakeEngine(r, registry, log) for r in range(world)]
+    monkeypatch.setattr(reshard, "get_engine", lambda device: engines[device])
+    group = _p2p_sim.ThreadGroup(world)
+    stats, errors = [None] * world, []
+
+    def worker(rank):
+        loop = asyncio.new_event_loop()
+        storage = storage_of(rank) if storage_of else FSStoragePlugin(root)
+        try:
+            stats[rank] = reshard.p2p_restore_units(units_of(rank), storage, group.view(rank), loop, rank)
+        except BaseException as e:  # noqa: B902
+            errors.append((rank, e))
+            if not expect_errors:
+                group._barrier.abort()
+        finally:
+            storage.sync_close(loop)
+            loop.close()
+
+    threads = [threading.Thread(target=worker, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=120)
+    assert all(not t.is_alive() for t in threads), "a rank is stuck"
+    assert all(not e.ctx.blocks for e in engines), "staging was not freed"
+    if expect_errors:
+        return errors
+    assert not errors, errors
+    return stats, log, engines
+
+
+def _layouts(world):
+    per, half, colw = ROWS // world, ROWS // world // 2, COLS // world
+    shifted = {}
+    for r in range(world):
+        boxes = [([(r * per + half) % ROWS, 0], [per - half if r == world - 1 else per, COLS])]
+        if r == world - 1:
+            boxes.append(([0, 0], [half, COLS]))
+        shifted[r] = boxes
+    return {
+        "row_to_column": {r: [([0, r * colw], [ROWS, colw])] for r in range(world)},
+        "rows_shifted": shifted,
+        "rows_same_cut": {r: [([r * per, 0], [per, COLS])] for r in range(world)},
+    }
+
+
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("layout", ["row_to_column", "rows_shifted", "rows_same_cut"])
+@pytest.mark.parametrize("scatter", ["1", "0"])
+def test_reshard_orchestration_on_cpu(tmp_path, monkeypatch, sharded_duck, world, layout, scatter):
+    monkeypatch.setenv("TSB200_P2P_SCATTER", scatter)
+    full = _cases.raw_tensor(5, [ROWS, COLS], torch.float32)
+    snap = _take(tmp_path, full, {"w": torch.arange(10.0)})
+    _manifest, merged = get_manifest_for_rank(snap.metadata, 0)
+    entry = merged["emb/t"]
+    assert len(entry.shards) == 12  # 4 saved shards x 3 pieces of 8 rows
+    dsts = {r: Sharded(_layouts(world)[layout][r]) for r in range(world)}
+    stats, log, _engines = _run_ranks(
+        world, snap.path, lambda r: reshard.sharded_units([("emb/t", entry, dsts[r])]), monkeypatch
+    )
+    for r in range(world):
+        for shard in dsts[r].local_shards():
+            want = _cases.box_slice(full, (shard.metadata.shard_offsets, shard.metadata.shard_sizes))
+            assert torch.equal(shard.tensor, want), (r, shard.metadata.shard_offsets)
+    total = ROWS * COLS * 4
+    assert sum(s.read_bytes for s in stats) == total  # every piece read from storage exactly once
+    assert sum(s.local_bytes + s.peer_bytes for s in stats) == total
+    assert all(s.launches == 1 for s in stats)
+    peer = sum(s.peer_bytes for s in stats)
+    if layout == "rows_same_cut":
+        assert peer == 0 and not [x for x in log if x[0] == "open"]
+    elif layout == "row_to_column":
+        assert peer == total * (world - 1) // world
+    exports = [x for x in log if x[0] == "export"]
+    if scatter == "1" and peer:
+        # reshard units never expose the owner's staging: what a peer maps is a buffer of its own, no larger
+        # than what it receives (plus alignment), and each is a driver allocation of its own
+        assert all(is_own for _k, _r, _n, is_own in exports)
+        assert sum(n for _k, _r, n, _o in exports) <= peer + 512 * 12 * world
+        assert sum(s.pack_launches for s in stats) > 0
+    elif scatter == "0" and peer:
+        assert sum(s.pack_launches for s in stats) == 0
+        assert sum(n for _k, _r, n, _o in exports) >= total - total // world  # whole staging blocks
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_replicated_units_are_shared_whole_and_mixed_with_a_reshard(tmp_path, monkeypatch, sharded_duck, world):
+    """Replicated state (every rank needs every byte) is read by one rank per unit and copied by the others
+    out of that rank's staging block; a reshard in the SAME call still goes through per-destination buffers."""
+    full = _cases.raw_tensor(6, [ROWS, COLS], torch.float32)
+    rep = {f"p{i}": _cases.raw_tensor(40 + i, [257 + i, 3], torch.float32) for i in range(6)}
+    snap = _take(tmp_path, full, rep)
+    manifest, merged = get_manifest_for_rank(snap.metadata, 0)
+    entry = merged["emb/t"]
+    colw = COLS // world if COLS % world == 0 else None
+    boxes = (lambda r: [([0, r * colw], [ROWS, colw])]) if colw else (lambda r: [([0, 0], [ROWS, COLS])] if r == 0 else [])
+    dsts = {r: Sharded(boxes(r)) for r in range(world)}
+    outs = {r: {k: torch.zeros_like(v) for k, v in rep.items()} for r in range(world)}
+
+    def units_of(r):
+        rrs = []
+        for k in rep:
+            reqs, _fut = prepare_read(manifest[f"rep/{k}"], obj_out=outs[r][k])
+            rrs += reqs
+        extra = reshard.read_req_units(batch_read_requests(rrs))
+        return list(reshard.sharded_units([("emb/t", entry, dsts[r])])) + list(extra)
+
+    stats, log, _engines = _run_ranks(world, snap.path, units_of, monkeypatch)
+    for r in range(world):
+        for k, v in rep.items():
+            assert torch.equal(outs[r][k], v), (r, k)
+        for shard in dsts[r].local_shards():
+            want = _cases.box_slice(full, (shard.metadata.shard_offsets, shard.metadata.shard_sizes))
+            assert torch.equal(shard.tensor, want)
+    rep_bytes = sum(v.numel() * 4 for v in rep.values())
+    assert sum(s.read_bytes for s in stats) == ROWS * COLS * 4 + rep_bytes  # nothing is read twice
+    shared = [x for x in log if x[0] == "export" and x[2] >= rep_bytes // world // 2 and x[3]]
+    assert shared, "the replicated staging block is exported as an allocation of its own"
+
+
+def test_a_failed_read_on_one_rank_raises_on_every_rank(tmp_path, monkeypatch, sharded_duck):
+    """Nobody may wait for bytes that will never arrive: the ranks agree on failure before the copy phase
+    (reference semantics would be an exception on the failing rank only -- and a hang in a collective here)."""
+    full = _cases.raw_tensor(8, [ROWS, COLS], torch.float32)
+    snap = _take(tmp_path, full, {"w": torch.arange(10.0)})
+    _manifest, merged = get_manifest_for_rank(snap.metadata, 0)
+    dsts = {r: Sharded(_layouts(2)["row_to_column"][r]) for r in range(2)}
+
+    class Broken(FSStoragePlugin):
+        async def read_into(self, path, byte_range, out):
+            raise OSError("disk on fire")
+
+    errors = _run_ranks(
+        2, snap.path, lambda r: reshard.sharded_units([("emb/t", merged["emb/t"], dsts[r])]), monkeypatch,
+        storage_of=lambda r: Broken(snap.path) if r == 1 else FSStoragePlugin(snap.path), expect_errors=True,
+    )
+    assert sorted(r for r, _e in errors) == [0, 1]
+    for _r, e in errors:
+        assert isinstance(e, RuntimeError) and "rank 1" in str(e) and "disk on fire" in str(e)
