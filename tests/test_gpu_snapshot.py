@@ -66,6 +66,46 @@ def test_c1_on_gpu_matches_reference_snapshot(golden_dir, tmp_path, engine):
     assert _bytes(st[2]["exp_avg_sq"]) == oracle.serialize(inputs["tensors"]["optim/state/2/exp_avg_sq"])
 
 
+def _to_cuda_like_default_adam(app_state):
+    """What a default (non-capturable) Adam leaves behind: parameters and moments on the GPU, `step` on the CPU."""
+    app_state["model"].cuda()
+    for st in app_state["optim"].state.values():
+        for k, v in st.items():
+            if isinstance(v, torch.Tensor) and k != "step":
+                st[k] = v.cuda()
+    return app_state
+
+
+def test_c1_with_adam_step_counters_on_the_cpu(golden_dir, tmp_path, engine):
+    """Mixed devices in one state dict (SURVEY 8d, config C2 variant): CPU members go to a CPU slab, CUDA
+    members to a GPU slab (batcher.py:291-319); every object's payload still equals the reference's, and the
+    snapshot restores into a state with the same device mix."""
+    ref_root = os.path.join(golden_dir, "c1_simple", "snapshot")
+    app_state = _to_cuda_like_default_adam(_c1_app_state(inputs=_c1_inputs(golden_dir)))
+    steps = [st["step"] for st in app_state["optim"].state.values()]
+    assert steps and all(isinstance(t, torch.Tensor) and not t.is_cuda for t in steps)
+    launches = engine.launches
+    ours = str(tmp_path / "snap")
+    snap = Snapshot.take(ours, app_state)
+    assert engine.launches > launches, "the CUDA path did not run"
+    ref_payloads, _ref_meta = _payloads(ref_root)
+    our_payloads, our_meta = _payloads(ours)
+    assert our_payloads == ref_payloads
+    tensors = {k: e for k, e in our_meta["manifest"].items() if e["type"] == "Tensor"}
+    step_files = {e["location"] for k, e in tensors.items() if k.endswith("/step")}
+    other_files = {e["location"] for k, e in tensors.items() if not k.endswith("/step")}
+    assert len(step_files) == 1 and len(other_files) == 1 and step_files != other_files  # one CPU slab, one GPU slab
+    fresh = _to_cuda_like_default_adam(_c1_app_state(seed=7))
+    snap.restore(fresh)
+    inputs = torch.load(os.path.join(golden_dir, "c1_simple", "inputs.pt"), weights_only=False)
+    for name, t in fresh["model"].state_dict().items():
+        assert t.is_cuda and _bytes(t) == oracle.serialize(inputs["tensors"][f"model/{name}"])
+    for idx, st in fresh["optim"].state_dict()["state"].items():
+        assert not st["step"].is_cuda and st["exp_avg"].is_cuda
+        for k in ("step", "exp_avg", "exp_avg_sq"):
+            assert _bytes(st[k]) == oracle.serialize(inputs["tensors"][f"optim/state/{idx}/{k}"]), (idx, k)
+
+
 @pytest.mark.parametrize("fs_direct", ["0", "1"])
 @pytest.mark.parametrize("case", ["mixed", "threshold"])
 def test_gpu_take_matches_reference_fixture(golden_dir, tmp_path, case, fs_direct, monkeypatch):
