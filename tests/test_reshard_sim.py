@@ -205,3 +205,23 @@ def test_a_failed_read_on_one_rank_raises_on_every_rank(tmp_path, monkeypatch, s
     assert sorted(r for r, _e in errors) == [0, 1]
     for _r, e in errors:
         assert isinstance(e, RuntimeError) and "rank 1" in str(e) and "disk on fire" in str(e)
+
+
+@pytest.mark.parametrize("layout", ["rows_shifted", "rows_same_cut"])
+def test_saved_by_four_restored_by_three(tmp_path, monkeypatch, sharded_duck, layout):
+    """A world size that does not divide the saved cut: 4 saved shards (12 pieces of 8 rows) restored into
+    3 row shards of 32 rows -- pieces straddle the new boundaries, so most units have two destinations."""
+    full = _cases.raw_tensor(9, [ROWS, COLS], torch.float32)
+    snap = _take(tmp_path, full, {"w": torch.arange(10.0)})
+    _manifest, merged = get_manifest_for_rank(snap.metadata, 0)
+    dsts = {r: Sharded(_layouts(3)[layout][r]) for r in range(3)}
+    stats, _log, _engines = _run_ranks(
+        3, snap.path, lambda r: reshard.sharded_units([("emb/t", merged["emb/t"], dsts[r])]), monkeypatch
+    )
+    for r in range(3):
+        for shard in dsts[r].local_shards():
+            want = _cases.box_slice(full, (shard.metadata.shard_offsets, shard.metadata.shard_sizes))
+            assert torch.equal(shard.tensor, want), (r, shard.metadata.shard_offsets)
+    assert sum(s.read_bytes for s in stats) == ROWS * COLS * 4
+    if layout == "rows_same_cut":  # 32-row shards are unions of whole 8-row pieces: every piece has one destination
+        assert sum(s.peer_bytes for s in stats) == 0
