@@ -235,6 +235,14 @@ int tsb_memcpy_d2d(TsbCtx* ctx, int stream, uint64_t dst, uint64_t src, uint64_t
  * BatchedBufferConsumer (batcher.py:364-375).
  */
 int tsb_host_memcpy(void* dst, const void* src, uint64_t nbytes, int nthreads);
+/*
+ * `count` independent host copies dst[i] <- src[i] (nbytes[i] bytes each; host addresses), balanced over
+ * `nthreads` workers by bytes.  The CPU-tensor side of the path: fills a host slab from its member tensors
+ * (BatchedBufferStager.stage_buffer, batcher.py:63-90: a zero-filled bytearray plus one interpreted slice
+ * assignment per member on the event-loop thread) and scatters a slab that was read back into its member
+ * tensors (BatchedBufferConsumer.consume_buffer, batcher.py:364-375 + tensor.py:329-338).
+ */
+int tsb_host_gather(const uint64_t* dst, const uint64_t* src, const uint64_t* nbytes, uint64_t count, int nthreads);
 
 /* ---- peer access (resharding over NVLink) ---------------------------------------------- */
 

@@ -100,3 +100,25 @@ def test_file_direct_flag_never_changes_the_bytes(tmp_path):
         _native.file_write(str(tmp_path / "x"), aligned.ctypes.data, 16, 1, 0x80)
     del aligned, arr
     page.close()
+
+
+def test_host_gather_splits_work_by_bytes():
+    # many copies of very different sizes, more threads than large copies: every byte lands once, nothing else moves
+    import numpy as np
+
+    rs = np.random.RandomState(3)
+    sizes = [0, 1, 7, 4096, 100003, 5 << 20, 33 << 20, 12345, 64, 63]
+    srcs = [rs.randint(0, 256, size=n).astype(np.uint8) for n in sizes]
+    total = sum(sizes)
+    for nthreads in (1, 3, 8):
+        slab = np.full(total + 8, 0xAB, dtype=np.uint8)
+        offs = np.concatenate([[0], np.cumsum(sizes)[:-1]])
+        _native.host_gather([slab.ctypes.data + 4 + int(o) for o in offs],
+                            [a.ctypes.data if a.nbytes else 0 for a in srcs], sizes, nthreads)
+        assert slab[4 : 4 + total].tobytes() == b"".join(a.tobytes() for a in srcs)
+        assert slab[:4].tobytes() == b"\xab" * 4 and slab[4 + total :].tobytes() == b"\xab" * 4
+    _native.host_gather([], [], [])  # nothing to do
+    with pytest.raises(_native.TsbError):
+        _native.host_gather([0], [srcs[3].ctypes.data], [16])
+    with pytest.raises(ValueError):
+        _native.host_gather([1, 2], [1], [1])

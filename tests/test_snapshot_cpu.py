@@ -249,3 +249,58 @@ def test_pickled_dtypes_round_trip(tmp_path):
     assert torch.equal(got, state["z"])
     with pytest.raises(RuntimeError, match="quantized"):
         snap.read_object("0/st/q")  # no runtime object to learn the quantization parameters from
+
+
+def test_host_slab_buffers_are_pooled_and_never_shared_while_viewed():
+    """CPU slabs and host reads use pooled buffers (batcher.HostSlab): a buffer goes back to the free list
+    only when the last memoryview of it is gone, and is then handed out again."""
+    import gc
+
+    from torchsnapshot_b200.batcher import HostSlab
+
+    n = (3 << 20) + 17
+    a = HostSlab(n)
+    view = memoryview(a)
+    assert len(view) == n and not view.readonly
+    ptr = a.ptr
+    view[:4] = b"abcd"
+    part = view[1:3]
+    del a, view
+    gc.collect()
+    b = HostSlab(n)  # `part` still pins the first buffer: this must be another one
+    assert b.ptr != ptr and bytes(part) == b"bc"
+    del part
+    gc.collect()
+    c = HostSlab(n)
+    assert c.ptr == ptr  # the released buffer is reused
+    del b, c
+
+
+def test_cpu_slab_fast_path_writes_the_reference_bytes(tmp_path):
+    """Members of every kind a CPU slab can hold -- dense, 0-d, strided views, bf16, bool -- through the native
+    gather (BatchedBufferStager) and the native scatter (BatchedBufferConsumer), against the oracle."""
+    import oracle
+
+    base = torch.arange(600, dtype=torch.float32).reshape(20, 30)
+    state = StateDict(
+        dense=torch.randn(1000), scalar=torch.tensor(3.5), strided=base[:, ::3], transposed=base.t(),
+        bf=torch.randn(64).bfloat16(), flags=torch.tensor([True, False, True]), i64=torch.arange(7),
+        inner=base[2:9, 4:11],
+    )
+    snap = Snapshot.take(str(tmp_path / "s"), {"st": state})
+    meta = json.load(open(os.path.join(snap.path, ".snapshot_metadata")))["manifest"]
+    files = {meta[f"0/st/{k}"]["location"] for k in state.keys()}
+    assert len(files) == 1  # one CPU slab
+    blob = open(os.path.join(snap.path, files.pop()), "rb").read()
+    for k, t in state.items():
+        lo, hi = meta[f"0/st/{k}"]["byte_range"]
+        assert blob[lo:hi] == oracle.serialize(t), k
+    # restore: dense destinations take the native scatter, the strided ones the per-member path
+    out = StateDict(
+        dense=torch.zeros(1000), scalar=torch.tensor(0.0), strided=torch.zeros(20, 30)[:, ::3],
+        transposed=torch.zeros(30, 20).t(), bf=torch.zeros(64).bfloat16(), flags=torch.zeros(3, dtype=torch.bool),
+        i64=torch.zeros(7, dtype=torch.int64), inner=torch.zeros(20, 30)[2:9, 4:11],
+    )
+    snap.restore({"st": out})
+    for k, t in state.items():
+        assert torch.equal(out[k], t), k

@@ -9,7 +9,7 @@ blocking waits may run in executor threads the way the reference runs its blocki
 import ctypes
 import os
 import threading
-from typing import Optional, Tuple
+from typing import Any, Optional, Tuple
 
 import numpy as np
 
@@ -79,6 +79,7 @@ _SIGNATURES = {
     "tsb_memcpy_h2d": (_i, [_p, _i, _u64, _p, _u64]),
     "tsb_memcpy_d2d": (_i, [_p, _i, _u64, _u64, _u64]),
     "tsb_host_memcpy": (_i, [_p, _p, _u64, _i]),
+    "tsb_host_gather": (_i, [_p, _p, _p, _u64, _i]),
     "tsb_ipc_export": (_i, [_p, _u64, _p, ctypes.POINTER(_u64)]),
     "tsb_ipc_open": (_i, [_p, _p, ctypes.POINTER(_u64)]),
     "tsb_ipc_close": (_i, [_p, _u64]),
@@ -288,6 +289,20 @@ def copy_regions_static(device: int, cuda_stream: int, regions: np.ndarray) -> N
 def host_memcpy(dst: int, src: int, nbytes: int, nthreads: int = 0) -> None:
     lib = load_library()
     _check(lib, lib.tsb_host_memcpy(dst, src, nbytes, nthreads))
+
+
+def host_gather(dst: Any, src: Any, nbytes: Any, nthreads: int = 0) -> None:
+    """dst[i] <- src[i] (nbytes[i] bytes) for every i: three equally long uint64 numpy arrays of host addresses
+    and lengths.  Runs without the GIL, on `nthreads` workers balanced by bytes."""
+    import numpy as np
+
+    d = np.ascontiguousarray(dst, dtype=np.uint64)
+    s_ = np.ascontiguousarray(src, dtype=np.uint64)
+    n = np.ascontiguousarray(nbytes, dtype=np.uint64)
+    if not (d.shape == s_.shape == n.shape and d.ndim == 1):
+        raise ValueError("host_gather: dst, src and nbytes must be 1-d arrays of one length")
+    lib = load_library()
+    _check(lib, lib.tsb_host_gather(d.ctypes.data, s_.ctypes.data, n.ctypes.data, d.shape[0], nthreads))
 
 
 FILE_DIRECT = 1  # TSB_FILE_DIRECT

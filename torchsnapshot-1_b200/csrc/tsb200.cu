@@ -1078,6 +1078,43 @@ int tsb_host_memcpy(void* dst, const void* src, uint64_t nbytes, int nthreads) {
   return TSB_OK;
 }
 
+// Many independent host copies (the members of a CPU slab) spread over worker threads by BYTES: the flat
+// byte range [0, total) of all copies is cut into equal shares, so one large member is split and many small
+// ones are grouped.
+int tsb_host_gather(const uint64_t* dst, const uint64_t* src, const uint64_t* nbytes, uint64_t count, int nthreads) {
+  if (count == 0) return TSB_OK;
+  if (!dst || !src || !nbytes) return set_err(TSB_EINVAL, "null argument");
+  uint64_t total = 0;
+  for (uint64_t i = 0; i < count; ++i) {
+    if (nbytes[i] && (!dst[i] || !src[i])) return set_err(TSB_EINVAL, "copy %llu: null address", (unsigned long long)i);
+    total += nbytes[i];
+  }
+  if (total == 0) return TSB_OK;
+  const int nt = default_threads(total, nthreads);
+  auto work = [=](uint64_t lo, uint64_t hi) {  // copies the bytes [lo, hi) of the flat range
+    uint64_t pos = 0;
+    for (uint64_t i = 0; i < count && pos < hi; ++i) {
+      const uint64_t n = nbytes[i];
+      const uint64_t a = std::max(lo, pos), b = std::min(hi, pos + n);
+      if (a < b) memcpy((char*)(uintptr_t)dst[i] + (a - pos), (const char*)(uintptr_t)src[i] + (a - pos), b - a);
+      pos += n;
+    }
+  };
+  if (nt <= 1) {
+    work(0, total);
+    return TSB_OK;
+  }
+  const uint64_t share = ((total + nt - 1) / nt + 63) / 64 * 64;
+  std::vector<std::thread> th;
+  for (int t = 0; t < nt; ++t) {
+    const uint64_t lo = (uint64_t)t * share;
+    if (lo >= total) break;
+    th.emplace_back(work, lo, std::min(total, lo + share));
+  }
+  for (auto& t : th) t.join();
+  return TSB_OK;
+}
+
 static int rw_range(int fd, bool write, char* buf, uint64_t off, uint64_t len) {
   while (len) {
     ssize_t k = write ? pwrite(fd, buf, len, (off_t)off) : pread(fd, buf, len, (off_t)off);

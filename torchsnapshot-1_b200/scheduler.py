@@ -569,9 +569,19 @@ async def execute_read_reqs(
         nonlocal bytes_read, budget, inflight_host
         try:
             async with io_slots:
-                read_io = ReadIO(path=rr.path, byte_range=rr.byte_range)
-                await storage.read(read_io=read_io)
-                buf = read_io.buf.getvalue()
+                read_into = getattr(storage, "read_into", None)
+                if read_into is not None and rr.byte_range is not None:
+                    # plugin fast path: the range lands in a pooled host buffer, no BytesIO / getvalue() copies
+                    from .batcher import HostSlab
+
+                    slab = HostSlab(rr.byte_range[1] - rr.byte_range[0])
+                    buf = memoryview(slab)
+                    del slab  # the view keeps the buffer alive; it returns to the pool with the last view
+                    await read_into(rr.path, rr.byte_range, buf)
+                else:
+                    read_io = ReadIO(path=rr.path, byte_range=rr.byte_range)
+                    await storage.read(read_io=read_io)
+                    buf = read_io.buf.getvalue()
             await rr.buffer_consumer.consume_buffer(buf, executor)
             bytes_read += len(buf)
         finally:
