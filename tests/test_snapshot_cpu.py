@@ -304,3 +304,34 @@ def test_cpu_slab_fast_path_writes_the_reference_bytes(tmp_path):
     snap.restore({"st": out})
     for k, t in state.items():
         assert torch.equal(out[k], t), k
+
+
+def test_large_cpu_tensors_are_read_straight_into_their_memory(tmp_path, monkeypatch):
+    """Tensors above the slab threshold are files of their own; a dense CPU destination of the saved dtype is
+    filled by the plugin's read_into directly (no staging buffer), chunked and tiled reads included."""
+    from torchsnapshot_b200 import knobs
+    from torchsnapshot_b200.storage_plugins import fs as fsmod
+
+    calls = []
+    orig = fsmod.FSStoragePlugin.read_into
+
+    async def spy(self, path, byte_range, out):
+        calls.append((path, byte_range, len(out)))
+        await orig(self, path, byte_range, out)
+
+    monkeypatch.setattr(fsmod.FSStoragePlugin, "read_into", spy)
+    big = torch.randn(300, 1000)
+    bf = torch.randn(70000).bfloat16()
+    state = StateDict(big=big, bf=bf, small=torch.arange(5.0))
+    with knobs.override_slab_size_threshold_bytes(100_000), knobs.override_max_chunk_size_bytes(500_000):
+        snap = Snapshot.take(str(tmp_path / "s"), {"st": state})
+        out = StateDict(big=torch.zeros(300, 1000), bf=torch.zeros(70000).bfloat16(), small=torch.zeros(5))
+        snap.restore({"st": out})
+    assert torch.equal(out["big"], big) and torch.equal(out["bf"], bf) and torch.equal(out["small"], state["small"])
+    sizes = sorted(n for _p, _r, n in calls)
+    assert 140000 in sizes  # the bf16 tensor, one read of exactly its bytes, into its own memory
+    assert sum(sizes) >= big.numel() * 4 + 140000  # the chunks of `big` arrived the same way
+    # random access with a memory budget: tiles are read into the tensor's own memory too
+    calls.clear()
+    got = snap.read_object("0/st/bf", obj_out=torch.zeros(70000).bfloat16(), memory_budget_bytes=30000)
+    assert torch.equal(got, bf) and len(calls) >= 5 and max(n for _p, _r, n in calls) <= 30000

@@ -31,6 +31,7 @@ from concurrent.futures import Executor, ThreadPoolExecutor
 from typing import Any, Dict, List, Optional, Set, Tuple
 
 import psutil
+import torch
 
 from . import _native, knobs
 from ._native import ArenaFull, STREAM_D2H, STREAM_H2D, STREAM_PACK
@@ -484,6 +485,25 @@ async def _read_into_pinned(
     await loop.run_in_executor(executor, _native.host_memcpy, pbuf.ptr, readonly_buffer_address(src), nbytes, 0)
 
 
+def _dense_host_destination(rr: ReadReq) -> Optional[Any]:
+    """The CPU tensor a read request fills when a raw byte copy of the stored range is the whole job (plain
+    tensor consumer, buffer-protocol entry, dense destination of the saved dtype and size); else None."""
+    from .batcher import _host_destination_of
+
+    consumer = rr.buffer_consumer
+    entry = getattr(consumer, "entry", None)
+    if entry is None or not hasattr(consumer, "tensor") or not hasattr(entry, "shape"):
+        return None
+    try:
+        nbytes = consumer.consumed_nbytes()
+    except Exception:
+        return None
+    if rr.byte_range is not None and rr.byte_range[1] - rr.byte_range[0] != nbytes:
+        return None
+    dst = _host_destination_of(consumer, nbytes)
+    return dst.reshape(-1).view(torch.uint8) if dst is not None else None
+
+
 async def execute_read_reqs(
     read_reqs: List[ReadReq],
     storage: StoragePlugin,
@@ -570,6 +590,13 @@ async def execute_read_reqs(
         try:
             async with io_slots:
                 read_into = getattr(storage, "read_into", None)
+                direct = _dense_host_destination(rr) if read_into is not None else None
+                if direct is not None:
+                    # one dense CPU tensor of the saved dtype and size: the file range IS its memory image,
+                    # so the plugin reads straight into the tensor (no intermediate buffer at all)
+                    await read_into(rr.path, rr.byte_range, memoryview(direct.numpy()))
+                    bytes_read += direct.numel()
+                    return
                 if read_into is not None and rr.byte_range is not None:
                     # plugin fast path: the range lands in a pooled host buffer, no BytesIO / getvalue() copies
                     from .batcher import HostSlab
