@@ -27,7 +27,6 @@ pytestmark = pytest.mark.skipif(not os.path.isdir(REF_TESTS), reason="reference 
 FAST = {
     "test_batcher.py": 120,
     "test_tensor_io_preparer.py": 5,
-    "test_chunked_tensor_io_preparer.py": 8,
     "test_serialization.py": 47,
     "test_manifest.py": 20,
     "test_flatten.py": 10,
@@ -36,7 +35,8 @@ FAST = {
     "test_sharded_tensor_resharding.py": 25,
     "test_rng_state.py": 1,
 }
-SLOW = {  # multi-process (torch.distributed.elastic launches), minutes each
+SLOW = {  # multi-process (torch.distributed.elastic launches) or multi-GiB tensors: up to minutes each
+    "test_chunked_tensor_io_preparer.py": 8,
     "test_sharded_tensor_io_preparer.py": 13,
     "test_read_object.py": 3,
     "test_async_take.py": 2,
