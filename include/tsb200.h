@@ -211,8 +211,14 @@ int tsb_copy_regions_timed(TsbCtx* ctx, int stream, const TsbRegion* regions, ui
  * short-run strided payload plus 128 B per such region) and the contiguous payload must fit
  * TSB_STATIC_MAX_TILES tiles of 32 KiB (1.5 GiB).  Split larger jobs into several calls on one stream.
  *
- * The first call on each device looks up the device address of the array (cudaGetSymbolAddress); make
- * that first call before any stream capture begins.  All calls share the array and it keeps whatever
+ * The first call on each device looks up the device address of the array (cudaGetSymbolAddress), which also
+ * makes the runtime load the library's device code and with it the array; make that first call early --
+ * before any stream capture begins, and before memory runs short if the call is meant for an
+ * out-of-memory path (a one-region copy of a few bytes will do).  A call on a stream that is being
+ * captured is refused with TSB_EINVAL.  Unlike the other entry points this one can block the host: the
+ * descriptors are uploaded from ordinary (pageable) memory, so the call returns only after the work queued
+ * on `cuda_stream` before it has finished and the upload has been handed to the copy engine; the copy
+ * kernels themselves run asynchronously.  All calls share the array and it keeps whatever
  * the previous call left in it; nothing needs zeroing because each call rewrites every entry it reads,
  * but two calls whose kernels can overlap on the GPU (different streams, no ordering between them)
  * race on it -- keep such calls on one stream or order them with events.

@@ -216,7 +216,9 @@ class Arena {
         for (int t = 1; t < nthreads; ++t) th.emplace_back(touch, t);
         touch(0);
         for (auto& t : th) t.join();
-        cudaError_t e = cudaHostRegister(q, n, cudaHostRegisterPortable);
+        // Mapped: SMs may store straight into the segment (the pack kernel writes host memory when no device
+        // staging is available); under unified addressing the device uses the host address as it is
+        cudaError_t e = cudaHostRegister(q, n, cudaHostRegisterPortable | cudaHostRegisterMapped);
         if (e == cudaSuccess) {
           mapped_[(uint64_t)(uintptr_t)q] = {(uint64_t)(uintptr_t)m, len};
           *base = (uint64_t)(uintptr_t)q;
@@ -227,7 +229,7 @@ class Arena {
       }
     }
     void* p = nullptr;
-    cudaError_t e = cudaHostAlloc(&p, n, cudaHostAllocPortable);
+    cudaError_t e = cudaHostAlloc(&p, n, cudaHostAllocPortable | cudaHostAllocMapped);
     *base = (uint64_t)(uintptr_t)p;
     return e;
   }
@@ -326,22 +328,37 @@ static int event_lookup(TsbCtx* ctx, TsbEvent h, cudaEvent_t* out) {
   return TSB_OK;
 }
 
-// free scratch of launches that have completed (caller holds no lock)
+// free scratch of launches that have completed (caller holds no lock).  With `wait_all` the launches still
+// in flight are waited for -- outside ctx->mu, so event records / queries of other threads never stall behind
+// a device wait.
 static void reap_scratch(TsbCtx* ctx, bool wait_all) {
-  std::vector<PendingScratch> done;
+  std::vector<PendingScratch> done, waiting;
   {
     std::lock_guard<std::mutex> g(ctx->mu);
     for (size_t i = 0; i < ctx->pending.size();) {
-      cudaError_t q = wait_all ? cudaEventSynchronize(ctx->pending[i].done) : cudaEventQuery(ctx->pending[i].done);
+      cudaError_t q = cudaEventQuery(ctx->pending[i].done);
       if (q == cudaErrorNotReady) {
-        ++i;
+        (void)cudaGetLastError();
+        if (wait_all) {
+          waiting.push_back(ctx->pending[i]);
+          ctx->pending.erase(ctx->pending.begin() + i);
+        } else {
+          ++i;
+        }
         continue;
       }
       if (q != cudaSuccess) (void)cudaGetLastError();
       done.push_back(ctx->pending[i]);
-      ctx->spare_scratch_events.push_back(ctx->pending[i].done);
       ctx->pending.erase(ctx->pending.begin() + i);
     }
+  }
+  for (auto& p : waiting) {
+    if (cudaEventSynchronize(p.done) != cudaSuccess) (void)cudaGetLastError();
+    done.push_back(p);
+  }
+  if (!done.empty()) {
+    std::lock_guard<std::mutex> g(ctx->mu);
+    for (auto& p : done) ctx->spare_scratch_events.push_back(p.done);
   }
   for (auto& p : done) {
     if (p.hbuf) ctx->scratch_host->free(p.hbuf);
@@ -460,7 +477,7 @@ static int build_tiles(const TsbRegion* regions, uint32_t n, TilePlan& plan) {
 // ------------------------------------------------------------------------------------------
 extern "C" {
 
-int tsb_version(void) { return 1000; }
+int tsb_version(void) { return 1001; }
 
 const char* tsb_last_error(void) { return g_err; }
 
@@ -594,14 +611,18 @@ int tsb_dev_alloc_exportable(TsbCtx* ctx, uint64_t nbytes, uint64_t* dptr) {
 
 int tsb_dev_free(TsbCtx* ctx, uint64_t dptr) {
   CHECK_CTX(ctx);
+  bool standalone = false;
   {
     std::lock_guard<std::mutex> g(ctx->mu);
     auto it = ctx->standalone.find(dptr);
     if (it != ctx->standalone.end()) {
       ctx->standalone.erase(it);
-      CUDA_TRY(cudaFree((void*)(uintptr_t)dptr));
-      return TSB_OK;
+      standalone = true;
     }
+  }
+  if (standalone) {  // cudaFree synchronises the device: never under ctx->mu
+    CUDA_TRY(cudaFree((void*)(uintptr_t)dptr));
+    return TSB_OK;
   }
   return ctx->dev_arena->free(dptr);
 }
@@ -644,7 +665,7 @@ int tsb_event_record(TsbCtx* ctx, int stream, TsbEvent* ev) {
   CHECK_CTX(ctx);
   CHECK_STREAM(stream);
   if (!ev) return set_err(TSB_EINVAL, "null argument");
-  uint32_t idx;
+  uint32_t idx = 0;
   cudaEvent_t e = nullptr;
   {
     std::lock_guard<std::mutex> g(ctx->mu);
@@ -653,7 +674,8 @@ int tsb_event_record(TsbCtx* ctx, int stream, TsbEvent* ev) {
       ctx->free_events.pop_back();
     } else {
       cudaEvent_t ne;
-      CUDA_TRY(cudaEventCreate(&ne));
+      cudaError_t ce = cudaEventCreate(&ne);
+      if (ce != cudaSuccess) return set_err(TSB_ECUDA, "cudaEventCreate failed: %s", cudaGetErrorString(ce));
       ctx->events.push_back(ne);
       ctx->event_gen.push_back(1);
       idx = (uint32_t)ctx->events.size();
@@ -661,7 +683,12 @@ int tsb_event_record(TsbCtx* ctx, int stream, TsbEvent* ev) {
     e = ctx->events[idx - 1];
     *ev = (uint64_t)idx | ((uint64_t)ctx->event_gen[idx - 1] << 32);
   }
-  CUDA_TRY(cudaEventRecord(e, ctx->streams[stream]));
+  cudaError_t re = cudaEventRecord(e, ctx->streams[stream]);
+  if (re != cudaSuccess) {
+    tsb_event_release(ctx, *ev);  // the slot goes back to the free list; the handle handed out is stale now
+    *ev = 0;
+    return set_err(TSB_ECUDA, "cudaEventRecord failed: %s", cudaGetErrorString(re));
+  }
   return TSB_OK;
 }
 
@@ -865,8 +892,21 @@ int tsb_copy_regions_timed(TsbCtx* ctx, int stream, const TsbRegion* regions, ui
   int rc = tsb_event_record(ctx, stream, kernel_start);
   if (rc != TSB_OK) return rc;
   rc = tsb_event_record(ctx, stream, kernel_stop);
-  if (rc != TSB_OK) return rc;
-  return copy_regions_impl(ctx, stream, regions, n, kernel_start, kernel_stop);
+  if (rc != TSB_OK) {
+    tsb_event_release(ctx, *kernel_start);
+    *kernel_start = 0;
+    return rc;
+  }
+  rc = copy_regions_impl(ctx, stream, regions, n, kernel_start, kernel_stop);
+  if (rc != TSB_OK) {  // the caller gets no handles on failure, so they must not stay allocated
+    char keep[sizeof(g_err)];
+    memcpy(keep, g_err, sizeof(keep));
+    tsb_event_release(ctx, *kernel_start);
+    tsb_event_release(ctx, *kernel_stop);
+    memcpy(g_err, keep, sizeof(keep));
+    *kernel_start = *kernel_stop = 0;
+  }
+  return rc;
 }
 
 int tsb_memcpy_d2h(TsbCtx* ctx, int stream, void* hptr, uint64_t dptr, uint64_t nbytes) {
@@ -939,6 +979,18 @@ extern "C" int tsb_copy_regions_static(int device, uint64_t cuda_stream, const T
     g_static_scratch_ready[device] = true;
   }
   unsigned char* const dscratch = static_cast<unsigned char*>(g_static_scratch_addr[device]);
+  {
+    // The descriptor upload below reads a host buffer that the next call overwrites, so a captured copy of
+    // this call would replay with whatever descriptors a later call left there: refuse instead.
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    cudaError_t ce = cudaStreamIsCapturing((cudaStream_t)(uintptr_t)cuda_stream, &cap);
+    if (ce != cudaSuccess) {
+      (void)cudaGetLastError();
+      return set_err(TSB_ECUDA, "cudaStreamIsCapturing failed: %s", cudaGetErrorString(ce));
+    }
+    if (cap != cudaStreamCaptureStatusNone)
+      return set_err(TSB_EINVAL, "tsb_copy_regions_static: the stream is being captured; call it outside the capture");
+  }
 
   // pass 1: count, so that an oversized request is refused before anything is written
   uint64_t n_runs = 0, n_flat_tiles = 0, n_str_tiles = 0, n_str_regions = 0;
@@ -1026,8 +1078,9 @@ extern "C" int tsb_copy_regions_static(int device, uint64_t cuda_stream, const T
   }
   if (ri == 0 && ti == 0) return TSB_OK;
   cudaStream_t s = (cudaStream_t)(uintptr_t)cuda_stream;
-  // pageable source: the runtime has consumed g_static_upload when this returns, so the buffer can be
-  // reused by the next call as soon as the mutex is released
+  // pageable source: the runtime first waits for the work already queued on the stream, then copies
+  // g_static_upload out before it returns -- so this call blocks the host for that long, and the buffer can
+  // be reused by the next call as soon as the mutex is released
   cudaError_t e = cudaMemcpyAsync(dscratch, g_static_upload, upload_need, cudaMemcpyHostToDevice, s);
   if (e == cudaSuccess && tiles) {
     TsbTile* dtiles = reinterpret_cast<TsbTile*>(dscratch + TSB_STATIC_UPLOAD_BYTES);

@@ -23,6 +23,7 @@ import os
 import socket
 import sys
 import threading
+import time
 from collections import defaultdict
 from concurrent.futures import ThreadPoolExecutor
 from typing import Any, Callable, Dict, List, Optional, Set, Tuple
@@ -62,6 +63,11 @@ logger: logging.Logger = logging.getLogger(__name__)
 
 SNAPSHOT_METADATA_FNAME = ".snapshot_metadata"
 VERSION = "0.1.0"  # the metadata schema version the reference writes (torchsnapshot/version.py:17)
+
+# wall-clock milliseconds of the phases of the last take on this rank, up to the point where take /
+# async_take hands over to the storage writes (what async_take's caller is blocked for): introspection for
+# bench.py and scripts/, a handful of clock reads per take
+last_take_phases: Dict[str, float] = {}
 
 
 
@@ -202,6 +208,15 @@ class Snapshot:
     ) -> Tuple[str, PendingIOWork, SnapshotMetadata, StoragePlugin]:
         rank, world = pg.get_rank(), pg.get_world_size()
         app_state = dict(app_state)
+        phases: Dict[str, float] = {}
+        t_mark = time.monotonic()
+
+        def mark(name: str) -> None:
+            nonlocal t_mark
+            now = time.monotonic()
+            phases[name] = phases.get(name, 0.0) + 1e3 * (now - t_mark)
+            t_mark = now
+
         # ---- collective 1: path, replication globs, keys, host ---------------------------------
         hello: List[Any] = [None] * world
         pg.all_gather_object(hello, (path, _infer_replicated(replicated, app_state), list(app_state.keys()),
@@ -214,6 +229,7 @@ class Snapshot:
         local_world = sum(1 for h in hello if h[3] == hello[rank][3])
         set_local_world_size(local_world)
         storage = url_to_storage_plugin(path, storage_options)
+        mark("hello_gather")
 
         # ---- state dicts -> flat leaves (RNG state first, restored afterwards) -----------------
         manifest: Manifest = {}
@@ -238,6 +254,7 @@ class Snapshot:
                 pg.barrier()  # state_dict() may run collectives; keep ranks in step
         if rng_items:
             rng_items[0][1].load_state_dict(rng_sd)
+        mark("state_dict_flatten")
 
         # ---- plan --------------------------------------------------------------------------------
         if "**" in globs:  # everything is replicated (benchmarks/ddp): no need to match 20 k paths one by one
@@ -260,6 +277,7 @@ class Snapshot:
             replicated_paths = {p for p in seen[0] if counts[p] == world}
         else:
             replicated_paths = set(candidates)
+        mark("replicated_paths_gather")
 
         object_entries: Dict[str, Entry] = {}
         write_reqs_by_path: Dict[str, List[WriteReq]] = {}
@@ -280,12 +298,15 @@ class Snapshot:
             else:
                 object_entries[logical_path] = entry
                 write_reqs_by_path[logical_path] = wrs
+        mark("prepare_write")
         object_entries, write_reqs_by_path = partition_write_reqs(object_entries, write_reqs_by_path, pg)
+        mark("partition_gather")
         write_reqs = [wr for wrs in write_reqs_by_path.values() for wr in wrs]
         if not knobs.is_batching_disabled():
             _, write_reqs = batch_write_requests(entries=list(object_entries.values()), write_reqs=write_reqs)
         manifest.update(primitive_entries)
         manifest.update(object_entries)
+        mark("batch")
 
         # ---- collective 3: the manifest ----------------------------------------------------------
         manifests: List[Any] = [None] * world
@@ -297,6 +318,7 @@ class Snapshot:
             prefix = f"{r}/"
             for logical_path, entry in m.items():
                 global_manifest[prefix + logical_path] = entry
+        mark("manifest_gather")
 
         pending = sync_execute_write_reqs(
             write_reqs=write_reqs,
@@ -305,6 +327,9 @@ class Snapshot:
             rank=rank,
             event_loop=event_loop,
         )
+        mark("stage")
+        global last_take_phases
+        last_take_phases = phases
         metadata = SnapshotMetadata(version=VERSION, world_size=world, manifest=global_manifest)
         return path, pending, metadata, storage
 
