@@ -208,3 +208,12 @@ def object_collectives(rank, world, tmp):
         assert "m/w" not in merged
     keep_all = consolidate_replicated_entries_dist(mine, pg, dedup=False)
     assert [c.offsets for c in keep_all["m/w"].chunks] == [[0, 0], [2, 0]]
+
+
+def elastic_roundtrip_cpu(rank, world, tmp):
+    """Taken by `world` ranks, restored by world/2 (a sub-group of the same job), taken again by those, restored
+    by all: flat parameters in two dtypes, a row-wise table, replicated state -- on CPU tensors over gloo."""
+    import _elastic
+
+    info = _elastic.elastic_roundtrip(tmp, "cpu")
+    assert info["world"] == world and info["half"] == max(world // 2, 1)

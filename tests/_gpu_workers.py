@@ -74,6 +74,14 @@ def p2p_reshard(rank, world, tmp):
     assert torch.equal(out_own["x"], own["x"])
     # a reshard goes through per-destination buffers (the owner packed this rank's columns for it) ...
     assert st.pack_launches > 0, vars(st)
+    assert abs(st.amplification["sharded"] - world) < 1e-6, st.amplification  # every rank would read every piece
+    # ... and the staging blocks and peer mappings of this restore serve the next one: nothing new from the driver
+    dst0 = _sharded(1, world, shape)
+    snap.restore({"emb": StateDict(t=dst0), "own": out_own})
+    st0 = reshard.last_stats
+    assert st0.new_staging_bytes == 0 and st0.opens == 0 and st0.peer_bytes == st.peer_bytes, vars(st0)
+    for a, b in zip(dst.local_shards(), dst0.local_shards()):
+        assert torch.equal(a.tensor, b.tensor)
     # ... and with that turned off every destination reads the owner's whole staging block: same bytes
     os.environ["TSB200_P2P_SCATTER"] = "0"
     try:
@@ -95,12 +103,24 @@ def p2p_reshard(rank, world, tmp):
             assert torch.equal(a.tensor, b.tensor)
     finally:
         del os.environ["TSB200_P2P_RESHARD"]
-    # row-wise -> row-wise at the same world size: no peer traffic at all
+    # row-wise -> row-wise at the same world size: the storage-only path reads every byte once as well, so
+    # every rank leaves the table to it (no staging, no peer traffic) ...
     dst3 = _sharded(0, world, shape)
     snap.restore({"emb": StateDict(t=dst3), "own": out_own})
-    assert reshard.last_stats.peer_bytes == 0 and reshard.last_stats.local_bytes == total // world
+    st3 = reshard.last_stats
+    assert st3.fell_back and st3.skipped_groups == ["sharded"] and st3.read_bytes == 0, vars(st3)
     for a, b in zip(src.local_shards(), dst3.local_shards()):
         assert torch.equal(a.tensor, b.tensor)
+    # ... unless told to share reads regardless: every rank then owns exactly its own pieces
+    os.environ["TSB200_P2P_MIN_AMPLIFICATION"] = "0"
+    try:
+        dst4 = _sharded(0, world, shape)
+        snap.restore({"emb": StateDict(t=dst4), "own": out_own})
+        assert reshard.last_stats.peer_bytes == 0 and reshard.last_stats.local_bytes == total // world
+        for a, b in zip(src.local_shards(), dst4.local_shards()):
+            assert torch.equal(a.tensor, b.tensor)
+    finally:
+        del os.environ["TSB200_P2P_MIN_AMPLIFICATION"]
 
 
 def ddp_replicated(rank, world, tmp):
@@ -177,3 +197,24 @@ def elastic_restore(rank, world, tmp):
         o, n = shard.metadata.shard_offsets[0], shard.metadata.shard_sizes[0]
         assert torch.equal(shard.tensor.cpu(), full[o : o + n]), (rank, o, n)
     assert torch.equal(rep["w"].cpu(), _cases.raw_tensor(901, [333, 7], torch.float32)) and rep["step"] == 5
+
+
+def elastic_roundtrip_gpu(rank, world, tmp):
+    """N -> N/2 -> N inside one job (tests/_elastic.py), on the GPUs: once the way the product decides (row-wise
+    re-cuts read nothing twice, so they go through storage on every rank; the replicated state is shared), and
+    once with every read shared, so that the re-cut shards cross NVLink where saved pieces straddle the new
+    boundaries.  Every restored shard is compared with the source pattern."""
+    import _elastic
+
+    sub = dist.new_group(ranks=list(range(max(world // 2, 1))))
+    info = _elastic.elastic_roundtrip(os.path.join(tmp, "a"), "cuda", sub=sub)
+    assert info["restore_at_n"] is not None and "sharded" in info["restore_at_n"]["skipped"], info
+    os.environ["TSB200_P2P_MIN_AMPLIFICATION"] = "0"
+    try:
+        info = _elastic.elastic_roundtrip(os.path.join(tmp, "b"), "cuda", sub=sub)
+        assert info["restore_at_n"]["p2p"], info
+        t = torch.tensor([info["restore_at_n"]["peer_bytes"]], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        assert t.item() > 0, "some shard boundary falls inside a saved piece, so some bytes cross NVLink"
+    finally:
+        del os.environ["TSB200_P2P_MIN_AMPLIFICATION"]

@@ -68,7 +68,10 @@ class FakeCtx:
         self.rank, self.registry, self.log = rank, registry, log
         self.blocks: Dict[int, np.ndarray] = {}
         self.exportable: set = set()
-        self.open_mappings: Dict[int, int] = {}
+        # peer mappings of every rank, shared through the registry: base address -> number of open mappings
+        self.mapped: Dict[int, int] = registry.setdefault(b"__mapped__", {})  # type: ignore[assignment]
+        self.fail_exportable = False  # dev_alloc_exportable raises (a rank that is out of HBM)
+        self.fail_open = False  # ipc_open raises (a peer allocation that cannot be mapped)
 
     # -- memory --
     def _alloc(self, nbytes: int) -> int:
@@ -81,12 +84,15 @@ class FakeCtx:
         return self._alloc(nbytes)
 
     def dev_alloc_exportable(self, nbytes: int) -> int:
+        if self.fail_exportable:
+            raise MemoryError("out of memory")
+        self.log.append(("alloc_exportable", self.rank, nbytes))
         addr = self._alloc(nbytes)
         self.exportable.add(addr)
         return addr
 
     def dev_free(self, addr: int) -> None:
-        assert not any(base == addr for base in self.open_mappings.values()), "freed while mapped"
+        assert not self.mapped.get(addr), "freed while a peer has it mapped"
         del self.blocks[addr]
         self.exportable.discard(addr)
 
@@ -101,12 +107,16 @@ class FakeCtx:
         raise AssertionError("export of an address that is not device memory")
 
     def ipc_open(self, handle: bytes) -> int:
+        if self.fail_open:
+            raise RuntimeError("invalid device context")
         base = self.registry[handle]
         self.log.append(("open", self.rank, handle[:4]))
+        self.mapped[base] = self.mapped.get(base, 0) + 1
         return base
 
     def ipc_close(self, base: int) -> None:
         self.log.append(("close", self.rank))
+        self.mapped[base] -= 1
 
     # -- streams / events: everything is synchronous here --
     def memcpy_h2d(self, stream: int, dst: int, src: int, nbytes: int) -> None:

@@ -62,3 +62,10 @@ def test_elastic_restore_at_another_world_size(tmp_path, new_world):
     re-cut for the loading ranks; replicated entries reach ranks that did not exist at save time."""
     _launch("elastic_take", tmp_path, world=2)
     _launch("elastic_restore", tmp_path, world=new_world)
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("world", [2, 4])
+def test_world_size_change_round_trip_inside_one_job(tmp_path, world):
+    """N -> N/2 -> N with a sub-group as the smaller world (what bench.py's pre-flight runs on the GPUs)."""
+    _launch("elastic_roundtrip_cpu", tmp_path, world=world)

@@ -57,3 +57,9 @@ def test_elastic_reshard_between_world_sizes(tmp_path, save_world, load_world):
     the peer-to-peer path when more than one rank loads), replicated state reaches new ranks."""
     _launch("elastic_take", tmp_path, world=save_world)
     _launch("elastic_restore", tmp_path, world=load_world)
+
+
+@pytest.mark.timeout(600)
+def test_world_size_change_round_trip_inside_one_job(tmp_path):
+    """2 -> 1 -> 2 with a sub-group as the smaller world (bench.py's pre-flight runs the same at N = 2, 4, 8)."""
+    _launch("elastic_roundtrip_gpu", tmp_path)

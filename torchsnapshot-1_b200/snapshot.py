@@ -355,11 +355,14 @@ class Snapshot:
         set_local_world_size(local_world)
         budget = _memory_budget(local_world)
         rng_key = rng_items[0][0] if rng_items else None
-        # keys every rank restores: only those can use the collective peer-to-peer reshard path
+        # keys every rank restores: only those can use the collective peer-to-peer reshard path -- and only
+        # inside one host: the payload moves through CUDA IPC mappings and NVLink, which end at the box.  A job
+        # that spans hosts restores the reference's way, every rank reading from storage what it needs.
         on_all_ranks = set.intersection(*(set(k[0]) for k in keys))
+        one_host = len({k[1] for k in keys}) == 1
         for key in global_keys:
             if key != rng_key:
-                p2p_pg = pg if (world > 1 and key in on_all_ranks and knobs.is_p2p_reshard_enabled()
+                p2p_pg = pg if (world > 1 and one_host and key in on_all_ranks and knobs.is_p2p_reshard_enabled()
                                 and torch.cuda.is_available()) else None
                 self._load_stateful(key, app_state.get(key), storage, rank, budget, event_loop, p2p_pg)
             if world > 1:
@@ -427,11 +430,20 @@ class Snapshot:
         if p2p_pg is not None and device >= 0:
             from . import reshard
 
+            shared_batched = shared_read_reqs
             if not knobs.is_batching_disabled():
-                shared_read_reqs = batch_read_requests(read_reqs=shared_read_reqs)
-            reshard.p2p_reshard_restore(
-                sharded_p2p, storage, p2p_pg, event_loop, device, extra_units=reshard.read_req_units(shared_read_reqs)
+                shared_batched = batch_read_requests(read_reqs=shared_read_reqs)
+            st = reshard.p2p_reshard_restore(
+                sharded_p2p, storage, p2p_pg, event_loop, device, extra_units=reshard.read_req_units(shared_batched)
             )
+            # what every rank alike left out of the shared-read path (reshard.py) takes the ordinary path
+            # below, each rank reading from storage what it needs
+            if st.fell_back or "replicated" in st.skipped_groups:
+                read_reqs += shared_read_reqs
+            if st.fell_back or "sharded" in st.skipped_groups:
+                for _logical_path, entry, obj_out in sharded_p2p:
+                    rrs, _fut = prepare_read(entry=entry, obj_out=obj_out)
+                    read_reqs += rrs
         if not knobs.is_batching_disabled():
             read_reqs = batch_read_requests(read_reqs=read_reqs)
         sync_execute_read_reqs(
