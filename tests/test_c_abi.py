@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_version_and_struct_layout():
     lib = _native.load_library()
-    assert lib.tsb_version() == 1000
+    assert lib.tsb_version() // 1000 == 1  # major version of the ABI
     assert _native.REGION_DTYPE.itemsize == 128
     assert _native.REGION_DTYPE.fields["size"][1] == 32
     assert _native.REGION_DTYPE.fields["src_stride"][1] == 64
