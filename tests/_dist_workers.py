@@ -217,3 +217,23 @@ def elastic_roundtrip_cpu(rank, world, tmp):
 
     info = _elastic.elastic_roundtrip(tmp, "cpu")
     assert info["world"] == world and info["half"] == max(world // 2, 1)
+
+
+def replicated_paths_differ(rank, world, tmp):
+    """`replicated=["**"]` with state dicts that differ between the ranks: only the paths every rank has are
+    replicated (reference snapshot.py:796-822).  The ranks find out in the partitioner's exchange (the digests of
+    their candidates differ), then exchange the candidate lists and plan again."""
+    import _cases
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    common = _cases.raw_tensor(31, [50, 9], torch.float32)
+    mine = _cases.raw_tensor(32 + rank, [20 + rank], torch.float32)
+    state = StateDict(common=common, **{f"only_{rank}": mine})
+    snap = Snapshot.take(os.path.join(tmp, "snap"), {"s": state}, replicated=["**"])
+    m = snap.get_manifest()
+    assert m["0/s/common"].replicated and "1/s/common" not in m
+    assert not m[f"{rank}/s/only_{rank}"].replicated
+    assert f"{1 - rank}/s/only_{rank}" not in m
+    out = StateDict(common=torch.zeros_like(common), **{f"only_{rank}": torch.zeros_like(mine)})
+    snap.restore({"s": out})
+    assert torch.equal(out["common"], common) and torch.equal(out[f"only_{rank}"], mine)

@@ -199,14 +199,15 @@ def elastic_restore(rank, world, tmp):
     assert torch.equal(rep["w"].cpu(), _cases.raw_tensor(901, [333, 7], torch.float32)) and rep["step"] == 5
 
 
-def elastic_roundtrip_gpu(rank, world, tmp):
+def elastic_roundtrip_gpu(rank, world, tmp, sub=None):
     """N -> N/2 -> N inside one job (tests/_elastic.py), on the GPUs: once the way the product decides (row-wise
     re-cuts read nothing twice, so they go through storage on every rank; the replicated state is shared), and
     once with every read shared, so that the re-cut shards cross NVLink where saved pieces straddle the new
     boundaries.  Every restored shard is compared with the source pattern."""
     import _elastic
 
-    sub = dist.new_group(ranks=list(range(max(world // 2, 1))))
+    if sub is None:
+        sub = dist.new_group(ranks=list(range(max(world // 2, 1))))
     info = _elastic.elastic_roundtrip(os.path.join(tmp, "a"), "cuda", sub=sub)
     assert info["restore_at_n"] is not None and "sharded" in info["restore_at_n"]["skipped"], info
     os.environ["TSB200_P2P_MIN_AMPLIFICATION"] = "0"

@@ -69,3 +69,8 @@ def test_elastic_restore_at_another_world_size(tmp_path, new_world):
 def test_world_size_change_round_trip_inside_one_job(tmp_path, world):
     """N -> N/2 -> N with a sub-group as the smaller world (what bench.py's pre-flight runs on the GPUs)."""
     _launch("elastic_roundtrip_cpu", tmp_path, world=world)
+
+
+@pytest.mark.timeout(300)
+def test_replicated_globs_over_state_dicts_that_differ_between_ranks(tmp_path):
+    _launch("replicated_paths_differ", tmp_path)

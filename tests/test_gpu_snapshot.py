@@ -214,6 +214,41 @@ def test_waves_and_small_arenas(tmp_path, monkeypatch):
         engmod.shutdown_engines()
 
 
+def test_no_device_staging_packs_into_and_unpacks_from_pinned_memory(tmp_path, monkeypatch):
+    """Requests larger than the device staging bound (or a trainer that has filled the HBM since the bound was
+    taken): the pack kernel stores straight into the pinned block and the unpack kernel reads straight out of
+    it -- no staging copy in HBM, same bytes.  The reference falls back to a CPU slab here (batcher.py:145-149)."""
+    from torchsnapshot_b200 import engine as engmod
+    from torchsnapshot_b200 import scheduler
+
+    engmod.shutdown_engines()
+    monkeypatch.setenv("TSB200_DEVICE_STAGING_BYTES", str(16 << 20))
+    try:
+        g = torch.Generator(device="cuda").manual_seed(5)
+        base = torch.randint(0, 2**31 - 1, (3000, 4096), dtype=torch.int32, device="cuda", generator=g)
+        state = StateDict(
+            dense=torch.randint(0, 255, (40 << 20,), dtype=torch.uint8, device="cuda", generator=g),  # > bound
+            view=base[:, ::2],  # 24 MiB, non-contiguous: strided source, host destination
+            small=torch.randn(1000, device="cuda", generator=g),
+        )
+        with knobs.override_slab_size_threshold_bytes(1 << 20):
+            snap = Snapshot.take(str(tmp_path / "s"), {"st": state})
+            assert scheduler.last_write_stats.host_packed_bytes == (40 << 20) + 3000 * 2048 * 4
+            for name, t in (("dense", state["dense"]), ("view", state["view"])):
+                assert (tmp_path / "s" / "0" / "st" / name).read_bytes() == _bytes(t), name
+            out_base = torch.zeros_like(base)
+            out = StateDict(dense=torch.zeros_like(state["dense"]), view=out_base[:, ::2], small=torch.zeros(1000, device="cuda"))
+            snap.restore({"st": out})
+            rs = scheduler.last_read_stats
+            assert rs.direct_bytes == 40 << 20  # the dense tensor: H2D straight into it
+            assert rs.host_unpacked_bytes == 3000 * 2048 * 4  # the strided one: unpack kernel reading pinned memory
+        for k in state:
+            assert torch.equal(out[k], state[k]), k
+        assert not out_base[:, 1::2].any(), "the unpack must not touch the elements between the view's columns"
+    finally:
+        engmod.shutdown_engines()
+
+
 def test_async_take_is_consistent_under_mutation(tmp_path):
     g = torch.Generator(device="cuda").manual_seed(1)
     state = StateDict({f"t{i}": torch.randn(1 << 18, device="cuda", generator=g) for i in range(40)})

@@ -45,8 +45,10 @@ def assign_write_loads(
         speed = [1.0] * len(sizes)
     else:
         mean = sum(rank_to_speed) / len(rank_to_speed)
-        # clamp: a noisy estimate must not starve or overload a rank
-        speed = [min(max(s / mean, 0.5), 2.0) for s in rank_to_speed]
+        # clamp: a noisy estimate must not starve or overload a rank.  The range follows what the boxes show:
+        # with 8 GPUs copying at once the slowest link ran at a quarter of the fastest (11.6 vs ~45 GB/s,
+        # profiles/r01_peaks_n8.txt)
+        speed = [min(max(s / mean, 0.25), 4.0) for s in rank_to_speed]
 
     def lightest() -> int:
         return min(range(len(sizes)), key=lambda r: (sizes[r] / speed[r], r))
@@ -82,6 +84,43 @@ def observed_speed() -> Optional[float]:
     return _speed_estimate
 
 
+def probe_speed(device: Optional[int] = None, nbytes: int = 256 << 20) -> Optional[float]:
+    """This rank's pinned device->host rate right now, from two copies of `nbytes` (CUDA events): the seed of
+    the speed estimate before the first take has been measured.  Every rank of a job reaches its first
+    partitioning at about the same time (right after a collective), so the probes overlap the way the copies of
+    the take will.  None when there is no device or no room for the probe's buffers."""
+    try:
+        import torch
+
+        if not torch.cuda.is_available():
+            return None
+        from ._native import STREAM_D2H
+        from .engine import get_engine
+
+        eng = get_engine(torch.cuda.current_device() if device is None else device)
+        ctx = eng.ctx
+        h = ctx.host_alloc(nbytes)
+        try:
+            d = ctx.dev_alloc(nbytes)
+            try:
+                ctx.memcpy_d2h(STREAM_D2H, h, d, nbytes)  # first touch of the path
+                a = ctx.event_record(STREAM_D2H)
+                ctx.memcpy_d2h(STREAM_D2H, h, d, nbytes)
+                ctx.memcpy_d2h(STREAM_D2H, h, d, nbytes)
+                b = ctx.event_record(STREAM_D2H)
+                ctx.event_sync(b)
+                ms = ctx.event_elapsed_ms(a, b)
+                ctx.event_release(a)
+                ctx.event_release(b)
+            finally:
+                ctx.dev_free(d)
+        finally:
+            ctx.host_free(h)
+        return 2 * nbytes / ms / 1e6 if ms > 0 else None
+    except Exception:  # noqa: BLE001 - a seed is optional
+        return None
+
+
 def record_take_speed(nbytes: int, device_ms: float) -> None:
     """Called by the scheduler when a take has drained: bytes moved / device time of pack + D2H."""
     global _speed_estimate
@@ -91,12 +130,34 @@ def record_take_speed(nbytes: int, device_ms: float) -> None:
     _speed_estimate = gbps if _speed_estimate is None else 0.5 * _speed_estimate + 0.5 * gbps
 
 
+class RanksDisagree(RuntimeError):
+    """Raised by partition_write_reqs on EVERY rank alike when the `agree_on` digests of the ranks differ."""
+
+
+def _digest(parts: Any) -> str:
+    import hashlib
+
+    h = hashlib.blake2b(digest_size=12)
+    for part in parts:
+        h.update(str(part).encode("utf-8"))
+        h.update(b"\n")
+    return h.hexdigest()
+
+
 def partition_write_reqs(
-    entries: Dict[str, Entry], write_reqs: Dict[str, List[WriteReq]], pg: Any
+    entries: Dict[str, Entry], write_reqs: Dict[str, List[WriteReq]], pg: Any, agree_on: Optional[str] = None
 ) -> Tuple[Dict[str, Entry], Dict[str, List[WriteReq]]]:
     """Keep, on this rank, only its share of the replicated write requests (reference
     partitioner.py:169-233).  Entries must be consolidated afterwards
-    (`consolidate_replicated_entries`)."""
+    (`consolidate_replicated_entries`).
+
+    One small all-gather in the common case: the ranks exchange a digest of their write loads (plus their
+    non-replicated bytes and measured device->host speed) and, when the digests agree -- replicated state is
+    the same on every rank by definition --, each computes the assignment from its own copy of the loads; only
+    ranks that disagree exchange the lists themselves, as the reference always does (partitioner.py:209-226).
+    `agree_on` is any string the caller wants compared across the ranks in the same exchange (snapshot.py sends
+    a digest of its replicated-path candidates and so saves a collective); if the ranks differ in it, every
+    rank raises RanksDisagree before anything is assigned."""
     if not set(write_reqs.keys()).issubset(entries.keys()):
         raise RuntimeError(
             "Not all entries associated with the write reqs are passed in. "
@@ -107,7 +168,9 @@ def partition_write_reqs(
     world = pg.get_world_size()
     rank = pg.get_rank()
     replicated = {k: v for k, v in entries.items() if is_replicated(v)}
-    if world == 1 or not replicated:
+    if world == 1 or (not replicated and agree_on is None):
+        # (with `agree_on` the exchange below is also the caller's agreement check: every rank takes part,
+        # whether or not it has replicated entries of its own)
         return entries, write_reqs
     non_replicated_size = sum(
         _write_req_size(wr) for k, wrs in write_reqs.items() if k not in replicated for wr in wrs
@@ -117,14 +180,26 @@ def partition_write_reqs(
         sub = getattr(entry, "type", None) == "ChunkedTensor"
         for idx, wr in enumerate(write_reqs.get(path, [])):
             loads.append((path, idx, _write_req_size(wr), sub))
+    global _speed_estimate
+    if _speed_estimate is None and any(
+        getattr(wr.buffer_stager, "is_device_stageable", lambda: False)()
+        for path in replicated for wr in write_reqs.get(path, [])[:1]
+    ):
+        # first take of replicated CUDA state in this process: measure instead of assuming equal links (the
+        # estimate is refined by every take from then on, record_take_speed)
+        _speed_estimate = probe_speed()
     gathered: List[Any] = [None] * world
-    pg.all_gather_object(gathered, (non_replicated_size, loads, observed_speed()))
-    # rank 0's view defines the units, like the reference; a chunked entry is only split when every
-    # rank chunked it identically
-    base_loads = gathered[0][1]
-    same = all(g[1] == base_loads for g in gathered)
-    if not same:
-        base_loads = [(p, i, s, False) for p, i, s, _sub in base_loads]
+    pg.all_gather_object(gathered, (non_replicated_size, _digest(loads), observed_speed(), agree_on))
+    if any(g[3] != gathered[0][3] for g in gathered):
+        raise RanksDisagree("the ranks do not agree on " + repr([g[3] for g in gathered]))
+    if all(g[1] == gathered[0][1] for g in gathered):
+        base_loads = loads
+    else:
+        # rank 0's view defines the units, like the reference; a chunked entry is only split when every
+        # rank chunked it identically
+        full: List[Any] = [None] * world
+        pg.all_gather_object(full, loads)
+        base_loads = [(p, i, s, False) for p, i, s, _sub in full[0]]
     speeds = [g[2] for g in gathered]
     mine = sorted(assign_write_loads(base_loads, [g[0] for g in gathered], speeds if all(speeds) else None)[rank])
     new_entries: Dict[str, Entry] = {k: v for k, v in entries.items() if k not in replicated}

@@ -44,7 +44,7 @@ from .manifest import (
     is_container_entry,
     is_replicated,
 )
-from .partitioner import consolidate_replicated_entries, partition_write_reqs
+from .partitioner import RanksDisagree, _digest as _paths_digest, consolidate_replicated_entries, partition_write_reqs
 from .pg_wrapper import PGWrapper
 from .scheduler import (
     PendingIOWork,
@@ -266,8 +266,42 @@ class Snapshot:
             ]
         else:
             candidates = []
-        if world > 1:
-            # ---- collective 2: which candidate paths exist on every rank ----------------------
+        max_chunk = knobs.get_max_chunk_size_bytes()
+
+        def plan(replicated_paths: Set[str]) -> Tuple[Dict[str, Entry], Dict[str, List[WriteReq]], Dict[str, Entry]]:
+            objects: Dict[str, Entry] = {}
+            wrs_by_path: Dict[str, List[WriteReq]] = {}
+            primitives: Dict[str, Entry] = {}
+            for logical_path, obj in flattened.items():
+                entry, wrs = prepare_write(
+                    obj,
+                    logical_path,
+                    rank,
+                    logical_path in replicated_paths,
+                    is_async,
+                    functools.partial(prepare_func, logical_path) if prepare_func else None,
+                    max_chunk,
+                )
+                if isinstance(entry, PrimitiveEntry):
+                    primitives[logical_path] = entry
+                else:
+                    objects[logical_path] = entry
+                    wrs_by_path[logical_path] = wrs
+            return objects, wrs_by_path, primitives
+
+        # ---- collective 2: which candidate paths exist on every rank, and who writes what ---------
+        # Replicated state has the same paths on every rank, so the plan is made for "all my candidates are
+        # replicated" and the partitioner's one exchange also carries a digest of the candidates.  Only when
+        # the ranks turn out to differ are the candidate lists themselves exchanged (the reference's way,
+        # snapshot.py:796-822) and the plan redone for the paths every rank has.
+        replicated_paths = set(candidates)
+        object_entries, write_reqs_by_path, primitive_entries = plan(replicated_paths)
+        mark("prepare_write")
+        try:
+            object_entries, write_reqs_by_path = partition_write_reqs(
+                object_entries, write_reqs_by_path, pg, agree_on=_paths_digest(candidates) if world > 1 else None
+            )
+        except RanksDisagree:
             seen: List[Any] = [None] * world
             pg.all_gather_object(seen, candidates)
             counts: Dict[str, int] = defaultdict(int)
@@ -275,31 +309,8 @@ class Snapshot:
                 for p in paths:
                     counts[p] += 1
             replicated_paths = {p for p in seen[0] if counts[p] == world}
-        else:
-            replicated_paths = set(candidates)
-        mark("replicated_paths_gather")
-
-        object_entries: Dict[str, Entry] = {}
-        write_reqs_by_path: Dict[str, List[WriteReq]] = {}
-        primitive_entries: Dict[str, Entry] = {}
-        max_chunk = knobs.get_max_chunk_size_bytes()
-        for logical_path, obj in flattened.items():
-            entry, wrs = prepare_write(
-                obj,
-                logical_path,
-                rank,
-                logical_path in replicated_paths,
-                is_async,
-                functools.partial(prepare_func, logical_path) if prepare_func else None,
-                max_chunk,
-            )
-            if isinstance(entry, PrimitiveEntry):
-                primitive_entries[logical_path] = entry
-            else:
-                object_entries[logical_path] = entry
-                write_reqs_by_path[logical_path] = wrs
-        mark("prepare_write")
-        object_entries, write_reqs_by_path = partition_write_reqs(object_entries, write_reqs_by_path, pg)
+            object_entries, write_reqs_by_path, primitive_entries = plan(replicated_paths)
+            object_entries, write_reqs_by_path = partition_write_reqs(object_entries, write_reqs_by_path, pg)
         mark("partition_gather")
         write_reqs = [wr for wrs in write_reqs_by_path.values() for wr in wrs]
         if not knobs.is_batching_disabled():
