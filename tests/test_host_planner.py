@@ -346,3 +346,123 @@ def test_merged_reads_stay_within_one_storage_object_size(monkeypatch):
     for r in merged:
         run(r.buffer_consumer.consume_buffer(payload[r.byte_range[0] : r.byte_range[1]]))
     assert bytes(t.numpy()) == payload
+
+
+def _plan_signature(entries):
+    """Entries with slab names replaced by the order in which the slabs first appear."""
+    names, out = {}, []
+    for path, e in entries.items():
+        names.setdefault(e.location, len(names))
+        br = tuple(e.byte_range) if e.byte_range is not None else None
+        out.append((path, names[e.location] if e.location.startswith("batched/") else e.location, br, e.dtype,
+                    tuple(e.shape), e.replicated, e.serializer, e.type))
+    return out
+
+
+@pytest.mark.parametrize("threshold", [4096, 40000, 1 << 20])
+def test_bulk_planner_gives_the_per_leaf_plan(threshold):
+    """batcher.plan_cuda_tensors (one vectorised pass) against prepare_write per tensor + batch_write_requests
+    (the reference-shaped planner, itself held to the reference's fixtures above): same entries, same slab
+    membership, same byte ranges, same stand-alone requests -- and the slabs' region tables, built by numpy,
+    equal the member-by-member ones, also for strided members, 0-d tensors and empty tensors."""
+    import numpy as np
+
+    from torchsnapshot_b200.batcher import GPUSlabStager, plan_cuda_tensors
+    from torchsnapshot_b200.regions import pack_regions, regions_to_array
+
+    rs = np.random.RandomState(3)
+    tensors = {}
+    for i in range(400):
+        kind = rs.randint(0, 10)
+        n = int(rs.randint(1, 6000))
+        if kind == 0:
+            t = torch.zeros(n, 6, dtype=torch.float32)[:, ::2]  # strided view
+        elif kind == 1:
+            t = torch.tensor(float(i))  # 0-d
+        elif kind == 2:
+            t = torch.zeros(0, 3)  # empty
+        elif kind == 3:
+            t = torch.zeros(n, dtype=torch.bfloat16)
+        elif kind == 4:
+            t = torch.zeros(max(n // 7, 1), 7, dtype=torch.int64)
+        else:
+            t = torch.zeros(n, dtype=torch.float32)
+        tensors[f"m/t{i}"] = t
+    paths = list(tensors)
+    replicated = [i % 5 == 0 for i in range(len(paths))]
+    storage = [("replicated/" if r else "3/") + p for p, r in zip(paths, replicated)]
+    bulk_entries, bulk_wrs = plan_cuda_tensors(paths, [tensors[p] for p in paths], storage, replicated, threshold)
+    leaf_entries, leaf_wrs = {}, []
+    for p, r in zip(paths, replicated):
+        e, w = prepare_write(tensors[p], p, 3, r)
+        leaf_entries[p] = e
+        leaf_wrs += w
+    _, leaf_wrs = batch_write_requests(list(leaf_entries.values()), leaf_wrs, threshold)
+    assert _plan_signature(bulk_entries) == _plan_signature(leaf_entries)
+    assert list(bulk_entries) == paths  # manifest order = the order given
+    # stand-alone requests: same paths, in order; slabs: same sizes, in order
+    solo = lambda wrs: [w.path for w in wrs if not w.path.startswith("batched/")]  # noqa: E731
+    assert solo(bulk_wrs) == solo(leaf_wrs)
+    slab_sizes = lambda wrs: [w.buffer_stager.slab_sz_bytes for w in wrs if w.path.startswith("batched/")]  # noqa: E731
+    assert slab_sizes(bulk_wrs) == slab_sizes(leaf_wrs)
+    # region tables: numpy-built == member by member
+    by_slab = {}
+    for p in paths:
+        e = bulk_entries[p]
+        if e.location.startswith("batched/"):
+            by_slab.setdefault(e.location, []).append((tensors[p], e.byte_range[0]))
+    base = 1 << 40
+    for w in bulk_wrs:
+        st = w.buffer_stager
+        if not isinstance(st, GPUSlabStager):
+            continue
+        want = []
+        for t, lo in by_slab[w.path]:
+            want += pack_regions(t, base + lo)
+        got = st.pack_region_array(base)
+        key = lambda a: sorted(map(bytes, a))  # noqa: E731  (the strided members come last in the numpy-built table)
+        assert key(got) == key(regions_to_array(want))
+        assert st.pack_regions(base) and len(st.pack_regions(base)) == len(want)
+
+
+def test_bulk_read_planner_gives_the_per_entry_reads():
+    """batcher.plan_cuda_reads against prepare_read per entry + batch_read_requests: the same merged ranges per
+    file (split at holes above 1 MiB), and region tables equal to the member-by-member ones."""
+    import numpy as np
+
+    from torchsnapshot_b200.batcher import plan_cuda_reads
+    from torchsnapshot_b200.regions import regions_to_array
+
+    rs = np.random.RandomState(4)
+    items = []
+    for f in range(3):
+        cursor = 0
+        for i in range(60):
+            n = int(rs.randint(1, 5000))
+            strided = i % 9 == 0
+            t = torch.zeros(n, 4)[:, ::2] if strided else torch.zeros(n, 2)
+            nbytes = n * 2 * 4
+            if i % 20 == 19:
+                cursor += 3 << 20  # a hole: members the restoring state dict does not ask for
+            e = TensorEntry(location=f"batched/f{f}", serializer="buffer_protocol", dtype="torch.float32",
+                            shape=[n, 2], replicated=False, byte_range=[cursor, cursor + nbytes])
+            items.append((e, t))
+            cursor += nbytes
+    order = rs.permutation(len(items)).tolist()
+    items = [items[i] for i in order]
+    bulk = plan_cuda_reads(items)
+    leaf = []
+    for e, t in items:
+        rrs, _fut = prepare_read(e, t)
+        leaf += rrs
+    leaf = batch_read_requests(leaf)
+    key = lambda rr: (rr.path, rr.byte_range)  # noqa: E731
+    assert sorted(map(key, bulk)) == sorted(map(key, leaf))
+    assert len(bulk) == 9  # 3 files x 3 runs between the holes
+    by_key = {key(rr): rr for rr in leaf}
+    base = 1 << 41
+    for rr in bulk:
+        want = regions_to_array(by_key[key(rr)].buffer_consumer.unpack_regions(base))
+        got = rr.buffer_consumer.unpack_region_array(base)
+        assert sorted(map(bytes, got)) == sorted(map(bytes, want))
+        assert rr.buffer_consumer.consumed_nbytes() == rr.byte_range[1] - rr.byte_range[0]

@@ -214,6 +214,247 @@ class GPUBatchedBufferStager(BatchedBufferStager):
         return self.slab_sz_bytes
 
 
+_new_object = object.__new__
+_BUFFER_PROTOCOL_VALUE = Serializer.BUFFER_PROTOCOL.value
+
+
+def _tensor_entry_class() -> Any:
+    from .manifest import TensorEntry
+
+    return TensorEntry
+
+
+class GPUSlabStager(BufferStager):
+    """A GPU slab planned in bulk (`plan_cuda_tensors`): the members are held as arrays of addresses, lengths and
+    slab offsets, so the region table of the pack launch is built by numpy, not member by member.  Same bytes
+    in the slab as GPUBatchedBufferStager, which the reference-shaped `batch_write_requests` still builds."""
+
+    def __init__(self, device: int, tensors: List[Any], ptrs: Any, offsets: Any, nbytes: Any, contiguous: Any,
+                 size: int) -> None:
+        self.device = device
+        self.tensors = tensors  # keeps the members alive until the slab has been packed
+        self._ptrs, self._offsets, self._nbytes, self._contiguous = ptrs, offsets, nbytes, contiguous
+        self.slab_sz_bytes = size
+
+    def is_device_stageable(self) -> bool:
+        return True
+
+    def staged_nbytes(self) -> int:
+        return self.slab_sz_bytes
+
+    def pack_region_array(self, dst_addr: int) -> Any:
+        """The slab's pack regions as a REGION_DTYPE array (members back to back at dst_addr)."""
+        import numpy as np
+
+        from .regions import pack_regions, regions_to_array
+
+        dense = self._contiguous & (self._nbytes > 0)
+        arr = np.zeros(int(dense.sum()), dtype=_native.REGION_DTYPE)
+        arr["src"] = self._ptrs[dense]
+        arr["dst"] = self._offsets[dense].astype(np.uint64) + np.uint64(dst_addr)
+        arr["run_bytes"] = self._nbytes[dense].astype(np.uint64)
+        strided = np.flatnonzero(~self._contiguous)
+        if strided.size:
+            regs: List[RegionTuple] = []
+            for i in strided:
+                regs += pack_regions(self.tensors[int(i)], dst_addr + int(self._offsets[i]))
+            arr = np.concatenate([arr, regions_to_array(regs)])
+        return arr
+
+    def pack_regions(self, dst_addr: int) -> List[RegionTuple]:
+        out: List[RegionTuple] = []
+        for rec in self.pack_region_array(dst_addr):
+            nd = int(rec["ndim"])
+            out.append((int(rec["src"]), int(rec["dst"]), int(rec["run_bytes"]), tuple(int(x) for x in rec["size"][:nd]),
+                        tuple(int(x) for x in rec["src_stride"][:nd]), tuple(int(x) for x in rec["dst_stride"][:nd])))
+        return out
+
+    async def stage_buffer(self, executor: Optional[Executor] = None) -> BufferType:
+        from .scheduler import stage_device_buffer
+
+        return await stage_device_buffer(self, self.device, executor)
+
+    def get_staging_cost_bytes(self) -> int:
+        return self.slab_sz_bytes
+
+
+def plan_cuda_tensors(
+    paths: List[str], tensors: List[Any], storage_paths: List[str], replicated: List[bool],
+    slab_size_threshold_bytes: Optional[int] = None, is_async_snapshot: bool = False,
+) -> Tuple[Dict[str, Any], List[WriteReq]]:
+    """Entries and write requests of plain CUDA tensors of buffer-protocol dtypes, planned in bulk.
+
+    The result is what TensorIOPreparer.prepare_write per tensor followed by batch_write_requests gives --
+    same TensorEntry fields, same slab membership and byte ranges (members back to back in the order given, a
+    new slab when `slab + tensor >= threshold`, reference batcher.py:291-316), tensors of `threshold` bytes or
+    more as requests of their own -- without a stager, a write request, a relocation record and a region tuple
+    per member: 13 k tensors plan in about a fifth of the time.  Callers (snapshot.py) use it only when every
+    member of the GPU slabs is planned here, so that the slabs are the ones the reference would form."""
+    import numpy as np
+
+    from .io_preparer import TensorBufferStager, _DTYPE_STRINGS
+    from .serialization import dtype_to_element_size
+
+    threshold = slab_size_threshold_bytes or knobs.get_slab_size_threshold_bytes()
+    T = torch.Tensor
+    entry_cls = _tensor_entry_class()
+    new, serializer = _new_object, _BUFFER_PROTOCOL_VALUE
+
+    def _tensor_entry(location: str, dtype: str, shape: List[int], rep: bool, byte_range: Optional[List[int]]) -> Any:
+        # TensorEntry without the dataclass constructor: this runs once per tensor of a 20 k-tensor state dict
+        e = new(entry_cls)
+        e.__dict__ = {"type": "Tensor", "location": location, "serializer": serializer, "dtype": dtype,
+                      "shape": shape, "replicated": rep, "byte_range": byte_range}
+        return e
+
+    n = len(tensors)
+    entries: Dict[str, Any] = {}
+    write_reqs: List[WriteReq] = []
+    if n == 0:
+        return entries, write_reqs
+    dtypes = [t.dtype for t in tensors]
+    nbytes = np.fromiter(map(T.numel, tensors), dtype=np.int64, count=n) * np.fromiter(
+        (dtype_to_element_size(d) for d in dtypes), dtype=np.int64, count=n)
+    ptrs = np.fromiter(map(T.data_ptr, tensors), dtype=np.uint64, count=n)
+    contiguous = np.fromiter(map(T.is_contiguous, tensors), dtype=np.bool_, count=n)
+    devices = np.fromiter(map(T.get_device, tensors), dtype=np.int64, count=n)
+    shapes = list(map(list, map(T.size, tensors)))
+    dtype_strs = [_DTYPE_STRINGS[d] for d in dtypes]
+    small = nbytes < threshold
+    # tensors of `threshold` bytes or more: a request each, in order (reference batcher.py:289-291)
+    for i in np.flatnonzero(~small):
+        i = int(i)
+        e = _tensor_entry(storage_paths[i], dtype_strs[i], shapes[i], replicated[i], None)
+        entries[paths[i]] = e
+        write_reqs.append(WriteReq(storage_paths[i], TensorBufferStager(tensors[i], e, is_async_snapshot, None)))
+    for dev in sorted(set(devices[small].tolist())):
+        idx = np.flatnonzero(small & (devices == dev))
+        sizes = nbytes[idx]
+        cum = np.cumsum(sizes)
+        start, m = 0, idx.size
+        while start < m:
+            before = int(cum[start - 1]) if start else 0
+            # member k joins while (bytes before it in the slab) + its own stay below the threshold
+            stop = int(np.searchsorted(cum, before + threshold, side="left"))
+            stop = max(stop, start + 1)
+            members = idx[start:stop]
+            offsets = cum[start:stop] - sizes[start:stop] - before
+            size = int(cum[stop - 1]) - before
+            location = os.path.join("batched", str(uuid.uuid4()))
+            lo_list, sz_list = offsets.tolist(), sizes[start:stop].tolist()
+            for k, i in enumerate(members.tolist()):
+                lo = lo_list[k]
+                entries[paths[i]] = _tensor_entry(location, dtype_strs[i], shapes[i], replicated[i], [lo, lo + sz_list[k]])
+            write_reqs.append(WriteReq(location, GPUSlabStager(
+                int(dev), [tensors[i] for i in members.tolist()], ptrs[members], offsets, sizes[start:stop],
+                contiguous[members], size)))
+            start = stop
+    # entries in the order the tensors were given (the manifest keeps insertion order)
+    return {p: entries[p] for p in paths}, write_reqs
+
+
+class GPUSlabConsumer(BufferConsumer):
+    """Mirror of GPUSlabStager for the read side (`plan_cuda_reads`): the members of one merged read of a slab
+    file, held as arrays; the region table of the unpack launch is built by numpy."""
+
+    def __init__(self, device: int, tensors: List[Any], ptrs: Any, offsets: Any, nbytes: Any, contiguous: Any,
+                 size: int) -> None:
+        self.device = device
+        self.tensors = tensors
+        self._ptrs, self._offsets, self._nbytes, self._contiguous = ptrs, offsets, nbytes, contiguous
+        self.buf_sz_bytes = size
+
+    def is_device_consumable(self) -> bool:
+        return True
+
+    def consumed_nbytes(self) -> int:
+        return self.buf_sz_bytes
+
+    def device_index(self) -> int:
+        return self.device
+
+    def unpack_region_array(self, src_addr: int) -> Any:
+        import numpy as np
+
+        from .regions import regions_to_array, unpack_regions
+
+        dense = self._contiguous & (self._nbytes > 0)
+        arr = np.zeros(int(dense.sum()), dtype=_native.REGION_DTYPE)
+        arr["src"] = self._offsets[dense].astype(np.uint64) + np.uint64(src_addr)
+        arr["dst"] = self._ptrs[dense]
+        arr["run_bytes"] = self._nbytes[dense].astype(np.uint64)
+        strided = np.flatnonzero(~self._contiguous)
+        if strided.size:
+            regs: List[RegionTuple] = []
+            for i in strided:
+                regs += unpack_regions(src_addr + int(self._offsets[i]), self.tensors[int(i)])
+            arr = np.concatenate([arr, regions_to_array(regs)])
+        return arr
+
+    def unpack_regions(self, src_addr: int) -> List[RegionTuple]:
+        out: List[RegionTuple] = []
+        for rec in self.unpack_region_array(src_addr):
+            nd = int(rec["ndim"])
+            out.append((int(rec["src"]), int(rec["dst"]), int(rec["run_bytes"]), tuple(int(x) for x in rec["size"][:nd]),
+                        tuple(int(x) for x in rec["src_stride"][:nd]), tuple(int(x) for x in rec["dst_stride"][:nd])))
+        return out
+
+    async def consume_buffer(self, buf: BufferType, executor: Optional[Executor] = None) -> None:
+        from .scheduler import consume_device_buffer
+
+        await consume_device_buffer(self, buf, self.device, executor)
+
+    def get_consuming_cost_bytes(self) -> int:
+        return self.buf_sz_bytes
+
+
+def plan_cuda_reads(items: List[Tuple[Any, Any]], max_merged_bytes: Optional[int] = None) -> List[ReadReq]:
+    """Read requests for slab members restored in place into plain CUDA tensors, planned in bulk: `items` are
+    (TensorEntry with a byte range, destination tensor of the entry's dtype and shape).  Gives the reads
+    TensorIOPreparer.prepare_read per entry followed by batch_read_requests gives -- the ranged reads of one
+    file merged into one read of [min lo, max hi), split at holes above 1 MiB and at the size bound -- with one
+    consumer per read instead of one per member."""
+    import numpy as np
+
+    limit = _MAX_MERGED_READ_BYTES if max_merged_bytes is None else max(int(max_merged_bytes), 1)
+    T = torch.Tensor
+    by_location: Dict[str, List[int]] = defaultdict(list)
+    for i, (entry, _t) in enumerate(items):
+        by_location[entry.location].append(i)
+    out: List[ReadReq] = []
+    for location, idxs in by_location.items():
+        idxs.sort(key=lambda i: items[i][0].byte_range[0])
+        los = [items[i][0].byte_range[0] for i in idxs]
+        his = [items[i][0].byte_range[1] for i in idxs]
+        groups: List[Tuple[int, int]] = []  # [a, b) into idxs
+        a, lo, hi = 0, los[0], his[0]
+        for k in range(1, len(idxs)):
+            if los[k] - hi > _MAX_READ_HOLE_BYTES or max(hi, his[k]) - lo > limit:
+                groups.append((a, k))
+                a, lo, hi = k, los[k], his[k]
+            else:
+                hi = max(hi, his[k])
+        groups.append((a, len(idxs)))
+        for a, b in groups:
+            members = idxs[a:b]
+            tensors = [items[i][1] for i in members]
+            lo = min(los[a:b])
+            hi = max(his[a:b])
+            n = len(members)
+            out.append(ReadReq(
+                path=location,
+                buffer_consumer=GPUSlabConsumer(
+                    int(tensors[0].get_device()), tensors,
+                    np.fromiter(map(T.data_ptr, tensors), dtype=np.uint64, count=n),
+                    np.asarray(los[a:b], dtype=np.int64) - lo,
+                    np.asarray(his[a:b], dtype=np.int64) - np.asarray(los[a:b], dtype=np.int64),
+                    np.fromiter(map(T.is_contiguous, tensors), dtype=np.bool_, count=n),
+                    hi - lo),
+                byte_range=(lo, hi),
+            ))
+    return out
+
+
 class SlabType(Enum):
     CPU = 0
     GPU = 1

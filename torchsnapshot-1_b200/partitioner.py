@@ -9,6 +9,7 @@ one all_gather_object instead of rank 0 computing and broadcasting it (one colle
 """
 
 import copy
+import math
 import os
 from collections import defaultdict
 from typing import Any, Dict, List, Optional, Sequence, Tuple
@@ -17,13 +18,20 @@ from .io_types import WriteReq
 from .manifest import ChunkedTensorEntry, Entry, is_replicated
 
 
+_ELEMENT_SIZES: Dict[str, int] = {}
+
+
 def _write_req_size(wr: WriteReq) -> int:
     stager = wr.buffer_stager
     entry = getattr(stager, "entry", None)
     if entry is not None and hasattr(entry, "dtype"):
-        from .io_preparer import TensorIOPreparer
+        # (this runs once per replicated tensor on the blocked path of every take)
+        es = _ELEMENT_SIZES.get(entry.dtype)
+        if es is None:
+            from .serialization import dtype_to_element_size, string_to_dtype
 
-        return TensorIOPreparer.get_tensor_size_from_entry(entry)
+            es = _ELEMENT_SIZES[entry.dtype] = dtype_to_element_size(string_to_dtype(entry.dtype))
+        return es * math.prod(entry.shape)
     return stager.get_staging_cost_bytes()
 
 
@@ -76,12 +84,28 @@ def assign_write_loads(
     return out
 
 
-_speed_estimate: Optional[float] = None  # this rank's device->host GB/s under load (EMA over takes)
+# This rank's throughput on its previous takes, GB/s: an EMA per KIND OF SINK (the class name of the storage
+# plugin the take wrote to).  What bounds a rank differs with the sink -- its host link when the sink is
+# faster than the link, the sink's own write path otherwise -- and so does the best split.
+_speed_estimates: Dict[str, float] = {}
+_speed_context: str = ""
+
+
+def set_speed_context(kind: str) -> None:
+    """Name the kind of sink of the take being planned (snapshot.py: the storage plugin's class name)."""
+    global _speed_context
+    _speed_context = kind
+
+
+def speed_context() -> str:
+    return _speed_context
 
 
 def observed_speed() -> Optional[float]:
-    """This rank's device->host throughput as measured on its previous takes (None before the first)."""
-    return _speed_estimate
+    """This rank's throughput as measured on its previous takes into this kind of sink; before the first,
+    the probed device->host rate (None if that could not be measured either)."""
+    got = _speed_estimates.get(_speed_context)
+    return got if got is not None else _speed_estimates.get("")
 
 
 def probe_speed(device: Optional[int] = None, nbytes: int = 256 << 20) -> Optional[float]:
@@ -121,13 +145,15 @@ def probe_speed(device: Optional[int] = None, nbytes: int = 256 << 20) -> Option
         return None
 
 
-def record_take_speed(nbytes: int, device_ms: float) -> None:
-    """Called by the scheduler when a take has drained: bytes moved / device time of pack + D2H."""
-    global _speed_estimate
-    if nbytes < (64 << 20) or device_ms <= 0:
-        return  # too small to say anything about the link
-    gbps = nbytes / device_ms / 1e6
-    _speed_estimate = gbps if _speed_estimate is None else 0.5 * _speed_estimate + 0.5 * gbps
+def record_take_speed(nbytes: int, ms: float, kind: Optional[str] = None) -> None:
+    """Called by the scheduler when a take has drained: this rank's payload bytes / the time from its first
+    pack launch to its last byte being handed to (and accepted by) the sink."""
+    if nbytes < (64 << 20) or ms <= 0:
+        return  # too small to say anything
+    kind = _speed_context if kind is None else kind
+    gbps = nbytes / ms / 1e6
+    prev = _speed_estimates.get(kind)
+    _speed_estimates[kind] = gbps if prev is None else 0.5 * prev + 0.5 * gbps
 
 
 class RanksDisagree(RuntimeError):
@@ -180,14 +206,15 @@ def partition_write_reqs(
         sub = getattr(entry, "type", None) == "ChunkedTensor"
         for idx, wr in enumerate(write_reqs.get(path, [])):
             loads.append((path, idx, _write_req_size(wr), sub))
-    global _speed_estimate
-    if _speed_estimate is None and any(
+    if observed_speed() is None and any(
         getattr(wr.buffer_stager, "is_device_stageable", lambda: False)()
         for path in replicated for wr in write_reqs.get(path, [])[:1]
     ):
         # first take of replicated CUDA state in this process: measure instead of assuming equal links (the
         # estimate is refined by every take from then on, record_take_speed)
-        _speed_estimate = probe_speed()
+        seed = probe_speed()
+        if seed:
+            _speed_estimates[""] = seed
     gathered: List[Any] = [None] * world
     pg.all_gather_object(gathered, (non_replicated_size, _digest(loads), observed_speed(), agree_on))
     if any(g[3] != gathered[0][3] for g in gathered):

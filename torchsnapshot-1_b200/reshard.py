@@ -357,7 +357,11 @@ class _PeerState:
             _other, size, base = min(fit)
             del self.free[base]
         else:
-            size = (max(nbytes, 1) + _POOL_GRANULE - 1) // _POOL_GRANULE * _POOL_GRANULE
+            # headroom: the units a rank owns shift a little from restore to restore (the writes of replicated
+            # state are re-partitioned by measured speed), and a block that is a few MiB short is a new
+            # cudaMalloc plus a new mapping on every peer
+            want = max(nbytes, 1) + (max(nbytes, 1) >> 2 if _POOL_GRANULE > 512 else 0)
+            size = (want + _POOL_GRANULE - 1) // _POOL_GRANULE * _POOL_GRANULE
             base = ctx.dev_alloc_exportable(size)
             stats.new_staging_bytes += size
         self._sizes[base] = size

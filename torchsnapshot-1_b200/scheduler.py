@@ -30,6 +30,7 @@ from collections import defaultdict
 from concurrent.futures import Executor, ThreadPoolExecutor
 from typing import Any, Dict, List, Optional, Set, Tuple
 
+import numpy as np
 import psutil
 import torch
 
@@ -132,6 +133,8 @@ class _Stats:
         self.bytes = 0
         self.staging_done: Optional[float] = None
         self.pack_launched: Optional[float] = None
+        self.first_pack_launched: Optional[float] = None
+        self.speed_context = ""  # kind of sink, for the partitioner's throughput history
         self.d2h_done: Optional[float] = None
         self.writes_done: Optional[float] = None
         # device-timed bracket of the take: first pack launch -> last D2H complete
@@ -286,10 +289,14 @@ class PendingIOWork:
         if knobs.trim_arenas_after_use():
             for eng in {e for e, _a, _b, _n in self.stats.pack_events}:
                 eng.ctx.arena_trim()
-        try:  # feed the replicated-write partitioner with this rank's measured device->host speed
+        try:  # feed the replicated-write partitioner with this rank's measured throughput into this kind of sink
             from .partitioner import record_take_speed
 
-            record_take_speed(self.stats.pack_kernel_bytes() // 2, self.stats.device_ms())
+            if self.stats.first_pack_launched is not None:
+                record_take_speed(
+                    self.stats.pack_kernel_bytes() // 2 + self.stats.host_packed_bytes,
+                    1e3 * (self.stats.writes_done - self.stats.first_pack_launched), self.stats.speed_context,
+                )
         except Exception:  # pragma: no cover - statistics only
             pass
         elapsed = max(self.stats.writes_done - self.stats.begin, 1e-9)
@@ -318,6 +325,12 @@ async def execute_write_reqs(
             pass
     stats = _Stats()
     last_write_stats = stats
+    try:
+        from .partitioner import speed_context
+
+        stats.speed_context = speed_context()
+    except Exception:  # pragma: no cover
+        pass
     tasks: Set["asyncio.Future[Any]"] = set()
     io_slots = asyncio.Semaphore(io_concurrency())
     alloc = _Allocator(memory_budget_bytes)
@@ -400,6 +413,8 @@ async def execute_write_reqs(
         stats.pack_events.append((eng, ev_start, ev_pack, 0))
         stats.d2h_end_events.append((eng, ctx.event_record(STREAM_PACK)))
         stats.pack_launched = time.monotonic()
+        if stats.first_pack_launched is None:
+            stats.first_pack_launched = stats.pack_launched
         stats.host_packed_bytes += n
         spawn(finish_file(eng, ctx.event_record(STREAM_PACK), pbuf, wr.path))
         return ev_pack
@@ -444,14 +459,25 @@ async def execute_write_reqs(
                     pack_waits.append((eng, ev_host))
                     await asyncio.sleep(0)
                     continue
-                regions = []
+                # region table of the wave: bulk-planned slabs hand over ready-made arrays
+                parts = []
+                regions: List[Any] = []
                 for wr, (_p, off, _n) in zip(wave_reqs, files):
-                    regions += wr.buffer_stager.pack_regions(base + off)
+                    as_array = getattr(wr.buffer_stager, "pack_region_array", None)
+                    if as_array is not None:
+                        if regions:
+                            parts.append(regions_to_array(regions))
+                            regions = []
+                        parts.append(as_array(base + off))
+                    else:
+                        regions += wr.buffer_stager.pack_regions(base + off)
+                if regions or not parts:
+                    parts.append(regions_to_array(regions))
                 if first:
                     eng.wait_current_stream(STREAM_PACK)
                     first = False
                 ev_start = ctx.event_record(STREAM_PACK)
-                arr = regions_to_array(regions)
+                arr = parts[0] if len(parts) == 1 else np.concatenate(parts)
                 if arr.shape[0]:
                     k0, k1 = eng.copy_region_array_timed(arr, STREAM_PACK)
                     stats.kernel_events.append((eng, k0, k1, 2 * sum(n for _p, _o, n in files)))
@@ -459,6 +485,8 @@ async def execute_write_reqs(
                 stats.pack_events.append((eng, ev_start, ev_pack, 2 * sum(n for _p, _o, n in files)))
                 pack_waits.append((eng, ev_pack))
                 stats.pack_launched = time.monotonic()
+                if stats.first_pack_launched is None:
+                    stats.first_pack_launched = stats.pack_launched
                 spawn(drain_wave(eng, base, files, ev_pack))
                 # give the drain a chance to queue its D2H copies before the next wave is planned
                 await asyncio.sleep(0)
@@ -604,7 +632,8 @@ async def execute_read_reqs(
                 io_slots.release()
                 slot_held = False
                 t_r = time.monotonic()
-                probe = consumer.unpack_regions(0)
+                # (a bulk-planned slab consumer is never a single dense destination worth probing for)
+                probe = consumer.unpack_regions(0) if not hasattr(consumer, "unpack_region_array") else []
                 if len(probe) == 1 and len(probe[0][3]) == 0 and probe[0][2] == nbytes and probe[0][0] == 0:
                     # one dense destination (a large tensor, a chunk): the H2D copy writes the tensor itself -- no
                     # staging block, no unpack pass (mirror of the dense case of stage_device_buffer)
@@ -635,7 +664,9 @@ async def execute_read_reqs(
                             ctx.event_release(ev_h2d)
                         else:
                             rstats.host_unpacked_bytes += nbytes
-                        arr = regions_to_array(consumer.unpack_regions(dptr if dptr is not None else pbuf.ptr))
+                        src_addr = dptr if dptr is not None else pbuf.ptr
+                        as_array = getattr(consumer, "unpack_region_array", None)
+                        arr = as_array(src_addr) if as_array is not None else regions_to_array(consumer.unpack_regions(src_addr))
                         k0 = k1 = None
                         if arr.shape[0]:
                             k0, k1 = eng.copy_region_array_timed(arr, STREAM_PACK)

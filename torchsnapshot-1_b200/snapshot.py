@@ -41,6 +41,7 @@ from .manifest import (
     PrimitiveEntry,
     ShardedTensorEntry,
     SnapshotMetadata,
+    TensorEntry,
     is_container_entry,
     is_replicated,
 )
@@ -95,6 +96,39 @@ def _infer_replicated(replicated: List[str], app_state: AppState) -> List[str]:
     return out
 
 
+def _bulk_plannable(
+    flattened: Dict[str, Any], replicated_paths: Set[str], world: int, prepare_func: Optional[Any], max_chunk: int
+) -> List[str]:
+    """Paths of the leaves batcher.plan_cuda_tensors plans (plain CUDA tensors of buffer-protocol dtypes that
+    are not chunked), or [] when the per-leaf planner has to do everything: bulk planning must cover EVERY
+    member of the GPU slabs, or the slabs would not be the ones the reference forms (batcher.py:291-316).  So
+    none of it when batching is off, a prepare function is set, chunks can be smaller than a slab, or some
+    would-be slab member cannot be planned here: a sharded tensor (its pieces join slabs), a tensor subclass,
+    replicated state of a multi-rank job (the partitioner assigns it request by request)."""
+    if prepare_func is not None or knobs.is_batching_disabled():
+        return []
+    threshold = knobs.get_slab_size_threshold_bytes()
+    if max_chunk < threshold:
+        return []
+    from .serialization import _BUFFER_PROTOCOL_SET
+
+    out: List[str] = []
+    tensor_types = (torch.Tensor, torch.nn.Parameter)
+    for path, obj in flattened.items():
+        kind = type(obj)
+        if kind in tensor_types:
+            if not obj.is_cuda or obj.dtype not in _BUFFER_PROTOCOL_SET:
+                continue
+            if world > 1 and path in replicated_paths:
+                return []
+            if obj.numel() * obj.element_size() > max_chunk:
+                continue  # chunked: the per-leaf planner (its chunks are at least a slab long here)
+            out.append(path)
+        elif _is_sharded_tensor(obj) or isinstance(obj, torch.Tensor):
+            return []
+    return out if len(out) >= 64 else []  # a handful of tensors plans just as fast the ordinary way
+
+
 @contextlib.contextmanager
 def _gc_paused():
     """Planning creates a few objects per tensor; a generational GC pass in the middle of it was the
@@ -114,6 +148,15 @@ def _memory_budget(local_world_size: int) -> int:
     import psutil
 
     return min(int(psutil.virtual_memory().available * 0.6) // max(local_world_size, 1), _MAX_PER_RANK_MEMORY_BUDGET_BYTES)
+
+
+class _Ready:
+    """A future that is already resolved: the object restored in place."""
+
+    __slots__ = ("obj",)
+
+    def __init__(self, obj: Any) -> None:
+        self.obj = obj
 
 
 class Snapshot:
@@ -229,6 +272,9 @@ class Snapshot:
         local_world = sum(1 for h in hello if h[3] == hello[rank][3])
         set_local_world_size(local_world)
         storage = url_to_storage_plugin(path, storage_options)
+        from .partitioner import set_speed_context
+
+        set_speed_context(type(storage).__name__)  # throughput history is kept per kind of sink
         mark("hello_gather")
 
         # ---- state dicts -> flat leaves (RNG state first, restored afterwards) -----------------
@@ -268,11 +314,29 @@ class Snapshot:
             candidates = []
         max_chunk = knobs.get_max_chunk_size_bytes()
 
+        bulk_write_reqs: List[WriteReq] = []
+
         def plan(replicated_paths: Set[str]) -> Tuple[Dict[str, Entry], Dict[str, List[WriteReq]], Dict[str, Entry]]:
             objects: Dict[str, Entry] = {}
             wrs_by_path: Dict[str, List[WriteReq]] = {}
             primitives: Dict[str, Entry] = {}
+            # plain CUDA tensors are planned in one vectorised pass when they are ALL of the GPU slabs' members
+            bulk_write_reqs.clear()
+            bulk = _bulk_plannable(flattened, replicated_paths, world, prepare_func, max_chunk)
+            bulk_entries: Dict[str, Entry] = {}
+            if bulk:
+                from .batcher import plan_cuda_tensors
+
+                bulk_entries, wrs = plan_cuda_tensors(
+                    bulk, [flattened[p] for p in bulk],
+                    [("replicated/" if p in replicated_paths else f"{rank}/") + p for p in bulk],
+                    [p in replicated_paths for p in bulk], None, is_async,
+                )
+                bulk_write_reqs.extend(wrs)
             for logical_path, obj in flattened.items():
+                if logical_path in bulk_entries:
+                    objects[logical_path] = bulk_entries[logical_path]
+                    continue
                 entry, wrs = prepare_write(
                     obj,
                     logical_path,
@@ -315,6 +379,7 @@ class Snapshot:
         write_reqs = [wr for wrs in write_reqs_by_path.values() for wr in wrs]
         if not knobs.is_batching_disabled():
             _, write_reqs = batch_write_requests(entries=list(object_entries.values()), write_reqs=write_reqs)
+        write_reqs += bulk_write_reqs  # GPU slabs last, like the reference (batcher.py:319)
         manifest.update(primitive_entries)
         manifest.update(object_entries)
         mark("batch")
@@ -406,13 +471,37 @@ class Snapshot:
         device = torch.cuda.current_device() if (p2p_pg is not None and torch.cuda.is_available()) else -1
         sharded_p2p: List[Tuple[str, ShardedTensorEntry, Any]] = []
         shared_read_reqs: List[ReadReq] = []
+        # slab members restored in place into plain CUDA tensors are planned in one pass (batcher.plan_cuda_reads);
+        # with thousands of small tensors the per-entry planner is most of the time before the first read starts
+        bulk_items: List[Tuple[Any, Any]] = []
+        bulk_ok = not knobs.is_batching_disabled()
+        tensor_types = (torch.Tensor, torch.nn.Parameter)
+        from .serialization import _STRING_TO_DTYPE, Serializer
+
+        buffer_protocol = Serializer.BUFFER_PROTOCOL.value
+        prefix_slash = prefix + "/"
         for logical_path, entry in manifest.items():
-            if logical_path.split("/")[0] != prefix:
+            if not logical_path.startswith(prefix_slash) and logical_path != prefix:
                 continue
             if is_container_entry(entry):
                 containers[logical_path] = entry
                 continue
             obj_out = flattened.get(logical_path)
+            if (
+                bulk_ok
+                and type(entry) is TensorEntry
+                and entry.byte_range is not None
+                and entry.serializer == buffer_protocol
+                and type(obj_out) in tensor_types
+                and obj_out.is_cuda
+                and not (device >= 0 and entry.replicated)
+                and _STRING_TO_DTYPE.get(entry.dtype) == obj_out.dtype
+                and entry.shape == list(obj_out.shape)
+            ):
+                bulk_items.append((entry, obj_out))
+                futs[logical_path] = _Ready(obj_out)
+                flattened.pop(logical_path, None)
+                continue
             if isinstance(entry, ShardedTensorEntry):
                 if obj_out is None:
                     continue  # sharded entries can only be loaded into a runtime object
@@ -457,6 +546,10 @@ class Snapshot:
                     read_reqs += rrs
         if not knobs.is_batching_disabled():
             read_reqs = batch_read_requests(read_reqs=read_reqs)
+        if bulk_items:
+            from .batcher import plan_cuda_reads
+
+            read_reqs += plan_cuda_reads(bulk_items)
         sync_execute_read_reqs(
             read_reqs=read_reqs, storage=storage, memory_budget_bytes=budget, rank=rank, event_loop=event_loop
         )
