@@ -458,7 +458,7 @@ def test_bulk_read_planner_gives_the_per_entry_reads():
     leaf = batch_read_requests(leaf)
     key = lambda rr: (rr.path, rr.byte_range)  # noqa: E731
     assert sorted(map(key, bulk)) == sorted(map(key, leaf))
-    assert len(bulk) == 9  # 3 files x 3 runs between the holes
+    assert len(bulk) == 12  # 3 files x 4 runs (three holes each)
     by_key = {key(rr): rr for rr in leaf}
     base = 1 << 41
     for rr in bulk:
