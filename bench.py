@@ -799,7 +799,7 @@ def main():
         line["suite"] = suite
         print(json.dumps(line), flush=True)
         shutil.rmtree(base, ignore_errors=True)
-    if world > 1:
+    if dist.is_initialized():
         dist.barrier(device_ids=[local_rank])
         dist.destroy_process_group()
     return 0
@@ -880,6 +880,26 @@ def run_suite(env):
                  "take_frac": round(tk / write_peak, 2), "restore_frac": round(rs / read_peak, 2), "parity": "ok"}
     del state, outs, app
     torch.cuda.empty_cache()
+
+    # ShardedTensor needs a process group even when the world is one rank (the legs above ran without one, like
+    # a single-process user of the library)
+    if world == 1 and not dist.is_initialized():
+        import socket
+
+        with socket.socket() as sock:
+            sock.bind(("127.0.0.1", 0))
+            port = sock.getsockname()[1]
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)  # NCCL's banner goes to stderr
+        try:
+            dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=0, world_size=1,
+                                    device_id=torch.device("cuda", local_rank))
+            dist.barrier(device_ids=[local_rank])
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
 
     # ---- C4 shape: FSDP-style flat sharded parameters; take at N, reshard-restore at N/2 -------------------
     total4 = min(16e9, 0.25 * tmpfs_free, 8e9 * world)

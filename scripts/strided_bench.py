@@ -36,3 +36,12 @@ rows(4, 8, 1 << 26, "elem_4B_stride2 (t[:, ::2])")
 m = src[: 8192 * 8192 * 4].view(torch.float32).view(8192, 8192)
 arr = regions_to_array(pack_regions(m.t(), dst.data_ptr()))
 timeit(arr, 8192 * 8192 * 4, "transpose_8192x8192_fp32", 2)
+# (r02) short runs whose source is misaligned by 1 / 4 bytes: 8- and 16-lane groups per run
+for run, shift in ((64, 1), (64, 4), (128, 1), (128, 2), (256, 1), (512, 1)):
+    rows(run, 8 * run, (1 << 28) // run, f"rows_{run}B_of_{8 * run}B_pitch_src_shift{shift}", shift=shift)
+# (r02) transposes of other element sizes, and a batched one (the tiled transpose kernel)
+for dt, es in ((torch.int16, 2), (torch.float64, 8)):
+    m2 = src[: 8192 * 8192 * es].view(dt).view(8192, 8192)
+    timeit(regions_to_array(pack_regions(m2.t(), dst.data_ptr())), 8192 * 8192 * es, f"transpose_8192x8192_{es}B_elements", 2)
+m3 = src[: 64 * 1024 * 1024 * 4].view(torch.float32).view(64, 1024, 1024)
+timeit(regions_to_array(pack_regions(m3.transpose(1, 2), dst.data_ptr())), 64 * 1024 * 1024 * 4, "transpose_batched_64x1024x1024_fp32", 2)

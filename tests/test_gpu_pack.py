@@ -162,6 +162,43 @@ def test_strided_rows_all_classes(engine, run_elems, rows, pitch_extra, dtype):
     assert _to_host(out.view(torch.uint8)) == want.view(torch.uint8).numpy().tobytes()
 
 
+@pytest.mark.parametrize("dtype", [torch.uint8, torch.int16, torch.float32, torch.float64])
+@pytest.mark.parametrize("shape", [(1000, 777), (64, 64), (17, 4099), (3, 130, 257), (5, 2, 70, 33)])
+def test_transposed_views_pack_and_unpack(engine, dtype, shape):
+    """Views whose fastest dimension differs between source and destination (x.t(), permutes of the last two
+    dims under batch dims): the tiled transpose kernel, packed against the oracle and unpacked into a
+    marker-filled twin; extents that are not multiples of the tile; and the element-by-element path
+    (TSB200_TRANSPOSE=0 is read once per process, so the plain strided kernel is checked through a region the
+    transpose class does not take: an extent below 16)."""
+    base = _cases.raw_tensor(31, list(shape), dtype)
+    perm = list(range(len(shape)))
+    perm[-1], perm[-2] = perm[-2], perm[-1]
+    view_c = base.permute(perm)
+    gbase = base.cuda()
+    view_g = gbase.permute(perm)
+    n = view_c.numel() * view_c.element_size()
+    slab = torch.full((n + 41,), 0x11, dtype=torch.uint8, device="cuda")
+    before = engine.ctx.counters()["kernel_launches"]
+    _launch(engine, pack_regions(view_g, slab.data_ptr() + 16))
+    assert engine.ctx.counters()["kernel_launches"] == before + 1  # the transpose kernel alone
+    got = _to_host(slab)
+    assert got[16 : 16 + n] == oracle.serialize(view_c)
+    assert got[:16] == b"\x11" * 16 and got[16 + n :] == b"\x11" * 25
+    out = torch.zeros_like(gbase).view(torch.uint8).fill_(0x77).view(dtype).reshape(gbase.shape)
+    _launch(engine, unpack_regions(slab.data_ptr() + 16, out.permute(perm)))
+    assert _to_host(out.view(torch.uint8)) == base.view(torch.uint8).numpy().tobytes()
+    # a strided column slice of the transposed view as the source, a pitched destination: both sides strided
+    if len(shape) == 2 and shape[0] >= 64:
+        src = gbase.t()[3:50:2]  # rows 3, 5, ... of the transposed view
+        dst = torch.zeros(src.shape[0], src.shape[1] + 5, dtype=dtype, device="cuda")
+        from torchsnapshot_b200.regions import box_regions
+
+        es = src.element_size()
+        _launch(engine, box_regions(src.data_ptr(), [x * es for x in src.stride()], dst.data_ptr(),
+                                    [x * es for x in dst.stride()], list(src.shape), es))
+        assert torch.equal(dst[:, : src.shape[1]].cpu(), base.t()[3:50:2]) and not dst[:, src.shape[1] :].any()
+
+
 def test_high_rank_views(engine):
     """5-d permuted view: more outer dims than one region holds, so the planner splits it."""
     base = _cases.raw_tensor(21, [3, 4, 5, 6, 7, 8], torch.int32)

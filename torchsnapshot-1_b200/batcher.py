@@ -281,6 +281,7 @@ class GPUSlabStager(BufferStager):
 def plan_cuda_tensors(
     paths: List[str], tensors: List[Any], storage_paths: List[str], replicated: List[bool],
     slab_size_threshold_bytes: Optional[int] = None, is_async_snapshot: bool = False,
+    max_chunk_size_bytes: Optional[int] = None,
 ) -> Tuple[Dict[str, Any], List[WriteReq]]:
     """Entries and write requests of plain CUDA tensors of buffer-protocol dtypes, planned in bulk.
 
@@ -321,8 +322,10 @@ def plan_cuda_tensors(
     shapes = list(map(list, map(T.size, tensors)))
     dtype_strs = [_DTYPE_STRINGS[d] for d in dtypes]
     small = nbytes < threshold
-    # tensors of `threshold` bytes or more: a request each, in order (reference batcher.py:289-291)
-    for i in np.flatnonzero(~small):
+    # tensors of `threshold` bytes or more: a request each, in order (reference batcher.py:289-291); those above
+    # the chunk size get no entry here -- the caller's per-leaf planner chunks them
+    chunked = nbytes > max_chunk_size_bytes if max_chunk_size_bytes is not None else np.zeros(n, dtype=np.bool_)
+    for i in np.flatnonzero(~small & ~chunked):
         i = int(i)
         e = _tensor_entry(storage_paths[i], dtype_strs[i], shapes[i], replicated[i], None)
         entries[paths[i]] = e
@@ -350,7 +353,7 @@ def plan_cuda_tensors(
                 contiguous[members], size)))
             start = stop
     # entries in the order the tensors were given (the manifest keeps insertion order)
-    return {p: entries[p] for p in paths}, write_reqs
+    return {p: entries[p] for p in paths if p in entries}, write_reqs
 
 
 class GPUSlabConsumer(BufferConsumer):

@@ -262,23 +262,31 @@ __device__ __forceinline__ void copy_vec_shifted(uint4* __restrict__ d4, const u
   }
 }
 
-// Cooperative byte-exact copy of n bytes by NL threads (lane in [0, NL)); NL >= 32.
+// Cooperative byte-exact copy of n bytes by a group of NL threads (lane in [0, NL)); NL = 8, 16 or 32.
 template <int NL>
 __device__ __forceinline__ void copy_span(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint64_t n,
                                           uint32_t lane) {
   if (n == 0) return;
   uint32_t head = (uint32_t)((16u - ((uint32_t)(uintptr_t)dst & 15u)) & 15u);
   if ((uint64_t)head > n) head = (uint32_t)n;
-  if (lane < head) dst[lane] = src[lane];
+  if (NL >= 16) {
+    if (lane < head) dst[lane] = src[lane];
+  } else {
+    for (uint32_t b = lane; b < head; b += NL) dst[b] = src[b];
+  }
   dst += head;
   src += head;
   n -= head;
   const uint64_t nvec = n >> 4;
   const uint32_t tail = (uint32_t)(n & 15u);
   // tail bytes by the last lanes, so head and tail do not serialise on the same threads
-  if (lane >= NL - tail) {
-    const uint64_t k = (nvec << 4) + (lane - (NL - tail));
-    dst[k] = src[k];
+  if (NL >= 16) {
+    if (lane >= NL - tail) {
+      const uint64_t k = (nvec << 4) + (lane - (NL - tail));
+      dst[k] = src[k];
+    }
+  } else {
+    for (uint32_t b = NL - 1 - lane; b < tail; b += NL) dst[(nvec << 4) + b] = src[(nvec << 4) + b];
   }
   if (nvec == 0) return;
   uint4* d4 = reinterpret_cast<uint4*>(dst);
@@ -355,7 +363,7 @@ template <typename T>
 __device__ __forceinline__ void copy_units(const TsbRegion* __restrict__ r, uint64_t src, uint64_t dst, uint32_t ndim,
                                            uint64_t first_unit, uint64_t nunits, uint32_t units_per_run,
                                            uint32_t tid, bool hint64) {
-  constexpr int U = 4;
+  constexpr int U = sizeof(T) >= 16 ? 2 : 4;  // 32-64 bytes in flight per thread either way
   for (uint64_t base = 0; base < nunits; base += (uint64_t)U * TSB_STRIDED_THREADS) {
     T v[U];
     T* dp[U];
@@ -383,6 +391,18 @@ __device__ __forceinline__ void copy_units(const TsbRegion* __restrict__ r, uint
 #pragma unroll
     for (int i = 0; i < U; ++i)
       if (ok[i]) *dp[i] = v[i];
+  }
+}
+
+// One run per group of NL lanes (the groups of a CTA take the runs of the tile round-robin).
+template <int NL>
+__device__ __forceinline__ void strided_runs(const TsbRegion* __restrict__ r, uint64_t src, uint64_t dst, uint32_t ndim,
+                                             uint64_t q0, uint32_t nruns, uint64_t run_bytes, uint32_t tid) {
+  const uint32_t group = tid / NL, lane = tid % NL;
+  for (uint32_t i = group; i < nruns; i += TSB_STRIDED_THREADS / NL) {
+    int64_t so, dofs;
+    run_offsets(r, ndim, q0 + i, so, dofs);
+    copy_span<NL>(reinterpret_cast<uint8_t*>(dst + dofs), reinterpret_cast<const uint8_t*>(src + so), run_bytes, lane);
   }
 }
 
@@ -414,17 +434,22 @@ tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __
   // 2.65 / 4.0-4.4 TB/s with 1 / 2 / 4 / 8-byte units whatever the run length, one-run-per-warp moves 0.75 /
   // 1.42 / 2.48 / 3.99 / 4.24 / 6.34 TB/s for runs of 64 / 128 / 256 / 512 / 1024 / 4096 bytes -- so the
   // warp form wins from 128 x unit bytes on.
+  // (r02) The group that takes a run is as wide as the run is long: 8 lanes up to 128 bytes, 16 up to 256, a whole
+  // warp above -- a warp per 64-byte run left 28 lanes idle (0.75 TB/s).  With groups, runs misaligned by 1, 2
+  // or 4 bytes take this form from 48 bytes on instead of crawling unit by unit (0.79 / 1.45 / 2.65 TB/s);
+  // 8-byte-aligned runs keep the unit form (4.0-4.4 TB/s) until the run form overtakes it (`warp_run_min` units).
   const uint32_t warp_run_min = warp_run_min_and_flags & 0x7fffffffu;
-  if (unit < 16u && run_bytes >= (uint64_t)warp_run_min * unit) {
+  const bool run_form = unit < 16u && (unit >= 8u ? run_bytes >= (uint64_t)warp_run_min * unit : run_bytes >= 48u);
+  if (run_form) {
     // the host emits whole runs per tile for this class
     const uint64_t q0 = off / run_bytes;
     const uint32_t nruns = len / (uint32_t)run_bytes;
-    const uint32_t warp = tid >> 5, lane = tid & 31u;
-    for (uint32_t i = warp; i < nruns; i += TSB_STRIDED_THREADS / 32) {
-      int64_t so, dofs;
-      run_offsets(r, ndim, q0 + i, so, dofs);
-      copy_span<32>(reinterpret_cast<uint8_t*>(dst + dofs), reinterpret_cast<const uint8_t*>(src + so), run_bytes,
-                    lane);
+    if (run_bytes <= 128u) {
+      strided_runs<8>(r, src, dst, ndim, q0, nruns, run_bytes, tid);
+    } else if (run_bytes <= 256u) {
+      strided_runs<16>(r, src, dst, ndim, q0, nruns, run_bytes, tid);
+    } else {
+      strided_runs<32>(r, src, dst, ndim, q0, nruns, run_bytes, tid);
     }
     return;
   }
@@ -438,5 +463,82 @@ tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __
     case 4: copy_units<uint32_t>(r, src, dst, ndim, first, nunits, upr, tid, hint64); break;
     case 8: copy_units<uint2>(r, src, dst, ndim, first, nunits, upr, tid, hint64); break;
     default: copy_units<uint4>(r, src, dst, ndim, first, nunits, upr, tid, hint64); break;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// transpose kernel
+// ---------------------------------------------------------------------------------------------
+// Boxes of single elements whose source is contiguous along one dimension and whose destination is contiguous
+// along ANOTHER one: a transposed view packed into a slab (x.t().contiguous() in the reference,
+// serialization.py:182-185), or a reshard between layouts whose fastest dimensions differ.  Element by element
+// one side of such a copy is always a gather of single elements (1.16 TB/s for fp32).  Here a CTA moves a square
+// tile through shared memory: loads run along the source's contiguous dimension, stores along the destination's.
+// The host permutes the region's dimensions so that the source-contiguous one is second to last and the
+// destination-contiguous one last (the order of a region's dimensions does not change what it copies) and sets
+// `reserved` to TSB_REGION_TRANSPOSE; tile `off` counts tiles: (batch index, tile along J, tile along L).
+#define TSB_REGION_TRANSPOSE 1u
+#define TSB_TRANSPOSE_THREADS 256
+#define TSB_TRANSPOSE_SMEM (64 * 65 * 8)
+
+__host__ __device__ __forceinline__ uint32_t tsb_transpose_tile(uint64_t elem_bytes) { return elem_bytes >= 16 ? 32u : 64u; }
+
+template <typename T, int TILE>
+__device__ __forceinline__ void transpose_tile(const TsbRegion* __restrict__ r, uint64_t src, uint64_t dst, uint32_t ndim,
+                                               uint64_t tile_id, unsigned char* smem_raw, uint32_t tid) {
+  T(*tile)[TILE + 1] = reinterpret_cast<T(*)[TILE + 1]>(smem_raw);
+  const uint32_t J = ndim - 2, L = ndim - 1;
+  const uint64_t nJ = __ldg(&r->size[J]), nL = __ldg(&r->size[L]);
+  const uint64_t tJ = (nJ + TILE - 1) / TILE, tL = (nL + TILE - 1) / TILE;
+  const uint64_t tl = tile_id % tL;
+  tile_id /= tL;
+  const uint64_t tj = tile_id % tJ;
+  uint64_t b = tile_id / tJ;
+  int64_t so = 0, dofs = 0;
+  for (int d = (int)ndim - 3; d >= 0; --d) {
+    const uint64_t sz = __ldg(&r->size[d]);
+    const uint64_t c = b % sz;
+    b /= sz;
+    so += (int64_t)c * __ldg(&r->src_stride[d]);
+    dofs += (int64_t)c * __ldg(&r->dst_stride[d]);
+  }
+  const uint64_t j0 = tj * TILE, l0 = tl * TILE;
+  const int64_t sL = __ldg(&r->src_stride[L]), dJ = __ldg(&r->dst_stride[J]);
+  const uint32_t wJ = (uint32_t)(nJ - j0 < TILE ? nJ - j0 : TILE), wL = (uint32_t)(nL - l0 < TILE ? nL - l0 : TILE);
+  const unsigned char* sp = reinterpret_cast<const unsigned char*>(src + so) + j0 * sizeof(T) + (int64_t)l0 * sL;
+  unsigned char* dp = reinterpret_cast<unsigned char*>(dst + dofs) + (int64_t)j0 * dJ + l0 * sizeof(T);
+  // in: consecutive threads along J (the source's contiguous dimension)
+  for (uint32_t i = tid; i < TILE * TILE; i += TSB_TRANSPOSE_THREADS) {
+    const uint32_t l = i / TILE, j = i % TILE;
+    if (j < wJ && l < wL) tile[l][j] = *reinterpret_cast<const T*>(sp + (uint64_t)j * sizeof(T) + (int64_t)l * sL);
+  }
+  __syncthreads();
+  // out: consecutive threads along L (the destination's contiguous dimension)
+  for (uint32_t i = tid; i < TILE * TILE; i += TSB_TRANSPOSE_THREADS) {
+    const uint32_t j = i / TILE, l = i % TILE;
+    if (j < wJ && l < wL) *reinterpret_cast<T*>(dp + (int64_t)j * dJ + (uint64_t)l * sizeof(T)) = tile[l][j];
+  }
+}
+
+__global__ void __launch_bounds__(TSB_TRANSPOSE_THREADS)
+tsb_copy_transpose_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __restrict__ tiles) {
+  __shared__ __align__(16) unsigned char smem[TSB_TRANSPOSE_SMEM];
+  const uint32_t tid = threadIdx.x;
+  const uint4 t1 = __ldg(reinterpret_cast<const uint4*>(tiles + blockIdx.x) + 1);
+  const uint64_t tile_id = ((uint64_t)t1.w << 32) | t1.z;
+  const TsbRegion* r = regions + t1.y;
+  const uint4* rp = reinterpret_cast<const uint4*>(r);
+  const uint4 ra = __ldg(rp);
+  const uint4 rb = __ldg(rp + 1);
+  const uint64_t src = ((uint64_t)ra.y << 32) | ra.x;
+  const uint64_t dst = ((uint64_t)ra.w << 32) | ra.z;
+  const uint32_t elem = rb.x;  // run_bytes: one element
+  const uint32_t ndim = rb.z;
+  switch (elem) {
+    case 1: transpose_tile<uint8_t, 64>(r, src, dst, ndim, tile_id, smem, tid); break;
+    case 2: transpose_tile<uint16_t, 64>(r, src, dst, ndim, tile_id, smem, tid); break;
+    case 4: transpose_tile<uint32_t, 64>(r, src, dst, ndim, tile_id, smem, tid); break;
+    case 8: transpose_tile<uint2, 64>(r, src, dst, ndim, tile_id, smem, tid); break;
+    default: transpose_tile<uint4, 32>(r, src, dst, ndim, tile_id, smem, tid); break;
   }
 }

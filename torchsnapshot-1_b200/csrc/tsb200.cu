@@ -419,8 +419,53 @@ struct TilePlan {
   uint64_t flat_tiles = 0;
   uint64_t payload = 0;
   std::vector<TsbTile> strided;
-  std::vector<TsbRegion> strided_regions;
+  std::vector<TsbTile> transposed;           // tiles of tsb_copy_transpose_kernel (`off` = tile number in its region)
+  std::vector<TsbRegion> strided_regions;    // regions of both tile lists
 };
+
+// A box of single elements that is contiguous along one dimension on the source side and along another on the
+// destination side (a transposed view being packed, a reshard between layouts with different fastest
+// dimensions): returns the region with its dimensions reordered to [the others..., J, L], J the source's
+// contiguous dimension and L the destination's, for tsb_copy_transpose_kernel.  TSB200_TRANSPOSE=0 turns the
+// class off (such boxes are then copied element by element by the strided kernel).
+static bool as_transpose(const TsbRegion& r, TsbRegion* out) {
+  static const bool enabled = [] {
+    const char* v = getenv("TSB200_TRANSPOSE");
+    return !(v && v[0] == '0');
+  }();
+  if (!enabled || r.ndim < 2) return false;
+  const uint64_t es = r.run_bytes;
+  if (es != 1 && es != 2 && es != 4 && es != 8 && es != 16) return false;
+  int J = -1, L = -1;
+  uint64_t misalign = r.src | r.dst;
+  for (uint32_t d = 0; d < r.ndim; ++d) {
+    misalign |= (uint64_t)r.src_stride[d] | (uint64_t)r.dst_stride[d];
+    if (r.src_stride[d] == (int64_t)es && r.dst_stride[d] != (int64_t)es && J < 0) J = (int)d;
+    if (r.dst_stride[d] == (int64_t)es && r.src_stride[d] != (int64_t)es) L = (int)d;
+  }
+  if (J < 0 || L < 0 || J == L || (misalign & (es - 1))) return false;
+  // worth a tile only when both extents fill a good part of it
+  if (r.size[J] < 16 || r.size[L] < 16) return false;
+  TsbRegion t = r;
+  uint32_t k = 0;
+  for (uint32_t d = 0; d < r.ndim; ++d) {
+    if ((int)d == J || (int)d == L) continue;
+    t.size[k] = r.size[d];
+    t.src_stride[k] = r.src_stride[d];
+    t.dst_stride[k] = r.dst_stride[d];
+    ++k;
+  }
+  t.size[k] = r.size[J];
+  t.src_stride[k] = r.src_stride[J];
+  t.dst_stride[k] = r.dst_stride[J];
+  ++k;
+  t.size[k] = r.size[L];
+  t.src_stride[k] = r.src_stride[L];
+  t.dst_stride[k] = r.dst_stride[L];
+  t.reserved = TSB_REGION_TRANSPOSE;
+  *out = t;
+  return true;
+}
 
 static int build_tiles(const TsbRegion* regions, uint32_t n, TilePlan& plan) {
   for (uint32_t i = 0; i < n; ++i) {
@@ -453,9 +498,27 @@ static int build_tiles(const TsbRegion* regions, uint32_t n, TilePlan& plan) {
       }
       continue;
     }
-    // short runs: tiles hold whole runs; the strided kernel walks them
     const uint32_t ridx = (uint32_t)plan.strided_regions.size();
+    TsbRegion tr;
+    if (as_transpose(r, &tr)) {
+      plan.strided_regions.push_back(tr);
+      const uint64_t tile = tsb_transpose_tile(r.run_bytes);
+      uint64_t count = ((tr.size[tr.ndim - 2] + tile - 1) / tile) * ((tr.size[tr.ndim - 1] + tile - 1) / tile);
+      for (uint32_t d = 0; d + 2 < tr.ndim; ++d) count *= tr.size[d];
+      for (uint64_t id = 0; id < count; ++id) {
+        TsbTile t;
+        t.src = 0;
+        t.dst = 0;
+        t.off = id;
+        t.len = 0;
+        t.region = ridx;
+        plan.transposed.push_back(t);
+      }
+      continue;
+    }
+    // short runs: tiles hold whole runs; the strided kernel walks them
     plan.strided_regions.push_back(r);
+    plan.strided_regions.back().reserved = 0;
     uint64_t runs_per_tile = TSB_TILE_BYTES / r.run_bytes;
     if (runs_per_tile == 0) runs_per_tile = 1;
     const uint64_t step = runs_per_tile * r.run_bytes;
@@ -791,14 +854,15 @@ static int copy_regions_impl(TsbCtx* ctx, int stream, const TsbRegion* regions, 
   plan.flat_runs.reserve(n);
   int rc = build_tiles(regions, n, plan);
   if (rc != TSB_OK) return rc;
-  if (plan.flat_runs.empty() && plan.strided.empty()) return TSB_OK;
-  if (plan.flat_tiles > 0x7fffffffull || plan.strided.size() > 0x7fffffffull)
+  if (plan.flat_runs.empty() && plan.strided.empty() && plan.transposed.empty()) return TSB_OK;
+  if (plan.flat_tiles > 0x7fffffffull || plan.strided.size() > 0x7fffffffull || plan.transposed.size() > 0x7fffffffull)
     return set_err(TSB_EINVAL, "too many tiles in one launch");
-  // uploaded scratch: [flat runs][strided tiles][strided regions]; device-only: [flat tiles]
+  // uploaded scratch: [flat runs][strided tiles][transpose tiles][regions of both]; device-only: [flat tiles]
   const uint64_t run_bytes = (uint64_t)plan.flat_runs.size() * sizeof(TsbRun);
   const uint64_t str_bytes = (uint64_t)plan.strided.size() * sizeof(TsbTile);
+  const uint64_t trn_bytes = (uint64_t)plan.transposed.size() * sizeof(TsbTile);
   const uint64_t reg_bytes = (uint64_t)plan.strided_regions.size() * sizeof(TsbRegion);
-  const uint64_t upload = run_bytes + str_bytes + reg_bytes;
+  const uint64_t upload = run_bytes + str_bytes + trn_bytes + reg_bytes;
   const uint64_t tile_bytes = plan.flat_tiles * sizeof(TsbTile);
   uint64_t hbuf = 0, dbuf = 0;
   rc = ctx->scratch_host->alloc(upload, &hbuf);
@@ -819,7 +883,8 @@ static int copy_regions_impl(TsbCtx* ctx, int stream, const TsbRegion* regions, 
   char* h = (char*)(uintptr_t)hbuf;
   if (run_bytes) memcpy(h, plan.flat_runs.data(), run_bytes);
   if (str_bytes) memcpy(h + run_bytes, plan.strided.data(), str_bytes);
-  if (reg_bytes) memcpy(h + run_bytes + str_bytes, plan.strided_regions.data(), reg_bytes);
+  if (trn_bytes) memcpy(h + run_bytes + str_bytes, plan.transposed.data(), trn_bytes);
+  if (reg_bytes) memcpy(h + run_bytes + str_bytes + trn_bytes, plan.strided_regions.data(), reg_bytes);
   cudaStream_t s = ctx->streams[stream];
   cudaError_t e = cudaMemcpyAsync((void*)(uintptr_t)dbuf, h, upload, cudaMemcpyHostToDevice, s);
   cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
@@ -839,17 +904,22 @@ static int copy_regions_impl(TsbCtx* ctx, int stream, const TsbRegion* regions, 
   } else if (kernel_start && event_lookup(ctx, *kernel_start, &ev_start) == TSB_OK) {
     cudaEventRecord(ev_start, s);
   }
+  const TsbRegion* d_regions = (const TsbRegion*)(uintptr_t)(dbuf + run_bytes + str_bytes + trn_bytes);
   if (e == cudaSuccess && !plan.strided.empty()) {
     tsb_copy_strided_kernel<<<(uint32_t)plan.strided.size(), TSB_STRIDED_THREADS, 0, s>>>(
-        (const TsbRegion*)(uintptr_t)(dbuf + run_bytes + str_bytes), (const TsbTile*)(uintptr_t)(dbuf + run_bytes),
-        warp_run_min());
+        d_regions, (const TsbTile*)(uintptr_t)(dbuf + run_bytes), warp_run_min());
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess && !plan.transposed.empty()) {
+    tsb_copy_transpose_kernel<<<(uint32_t)plan.transposed.size(), TSB_TRANSPOSE_THREADS, 0, s>>>(
+        d_regions, (const TsbTile*)(uintptr_t)(dbuf + run_bytes + str_bytes));
     e = cudaGetLastError();
   }
   if (kernel_stop && event_lookup(ctx, *kernel_stop, &ev_stop) == TSB_OK) cudaEventRecord(ev_stop, s);
   {
     std::lock_guard<std::mutex> g(ctx->mu);
     ctx->n_copy_calls += 1;
-    ctx->n_kernel_launches += (plan.flat_tiles ? 2 : 0) + (plan.strided.empty() ? 0 : 1);
+    ctx->n_kernel_launches += (plan.flat_tiles ? 2 : 0) + (plan.strided.empty() ? 0 : 1) + (plan.transposed.empty() ? 0 : 1);
     ctx->desc_upload_bytes += upload;
     ctx->kernel_payload_bytes += plan.payload;
   }
@@ -1073,7 +1143,8 @@ extern "C" int tsb_copy_regions_static(int device, uint64_t cuda_stream, const T
         t.region = (uint32_t)gi;
         stiles[ti++] = t;
       }
-      sregs[gi++] = r;
+      sregs[gi] = r;
+      sregs[gi++].reserved = 0;
     }
   }
   if (ri == 0 && ti == 0) return TSB_OK;

@@ -113,17 +113,17 @@ def _bulk_plannable(
     from .serialization import _BUFFER_PROTOCOL_SET
 
     out: List[str] = []
-    tensor_types = (torch.Tensor, torch.nn.Parameter)
+    plain, param = torch.Tensor, torch.nn.Parameter
+    check_replicated = world > 1 and bool(replicated_paths)
     for path, obj in flattened.items():
         kind = type(obj)
-        if kind in tensor_types:
-            if not obj.is_cuda or obj.dtype not in _BUFFER_PROTOCOL_SET:
-                continue
-            if world > 1 and path in replicated_paths:
-                return []
-            if obj.numel() * obj.element_size() > max_chunk:
-                continue  # chunked: the per-leaf planner (its chunks are at least a slab long here)
-            out.append(path)
+        if kind is plain or kind is param:
+            # (tensors above the chunk size are handed back by plan_cuda_tensors: their chunks are at least a
+            # slab long here, so they never join a slab)
+            if obj.is_cuda and obj.dtype in _BUFFER_PROTOCOL_SET:
+                if check_replicated and path in replicated_paths:
+                    return []
+                out.append(path)
         elif _is_sharded_tensor(obj) or isinstance(obj, torch.Tensor):
             return []
     return out if len(out) >= 64 else []  # a handful of tensors plans just as fast the ordinary way
@@ -327,10 +327,15 @@ class Snapshot:
             if bulk:
                 from .batcher import plan_cuda_tensors
 
+                own = f"{rank}/"
+                if replicated_paths:
+                    flags = [p in replicated_paths for p in bulk]
+                    storage_paths = [("replicated/" if r else own) + p for p, r in zip(bulk, flags)]
+                else:
+                    flags = [False] * len(bulk)
+                    storage_paths = [own + p for p in bulk]
                 bulk_entries, wrs = plan_cuda_tensors(
-                    bulk, [flattened[p] for p in bulk],
-                    [("replicated/" if p in replicated_paths else f"{rank}/") + p for p in bulk],
-                    [p in replicated_paths for p in bulk], None, is_async,
+                    bulk, [flattened[p] for p in bulk], storage_paths, flags, None, is_async, max_chunk
                 )
                 bulk_write_reqs.extend(wrs)
             for logical_path, obj in flattened.items():
