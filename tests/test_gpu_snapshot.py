@@ -251,6 +251,55 @@ def test_no_device_staging_packs_into_and_unpacks_from_pinned_memory(tmp_path, m
         engmod.shutdown_engines()
 
 
+def test_repeated_takes_reuse_the_plan_and_follow_changes(tmp_path):
+    """Checkpointing the same tensors again reuses the previous bulk plan (same entries, same slab layout); new
+    values in the same tensors are what gets saved; a tensor that was replaced, reshaped or re-strided makes the
+    planner start over.  Every snapshot restores to exactly what the state held when it was taken."""
+    from torchsnapshot_b200.batcher import take_plan_cache
+
+    g = torch.Generator(device="cuda").manual_seed(9)
+    state = StateDict({f"t{i}": torch.randn(100 + 3 * i, 5, device="cuda", generator=g) for i in range(90)})
+    state["view"] = torch.randn(64, 10, device="cuda", generator=g)[:, ::2]
+    state["n"] = 3
+
+    def check(snap, want):
+        out = StateDict({k: (torch.zeros_like(v) if isinstance(v, torch.Tensor) else 0) for k, v in want.items()})
+        snap.restore({"st": out})
+        for k, v in want.items():
+            assert torch.equal(out[k], v) if isinstance(v, torch.Tensor) else out[k] == v, k
+
+    with knobs.override_slab_size_threshold_bytes(1 << 16):
+        h0 = take_plan_cache.hits
+        s1 = Snapshot.take(str(tmp_path / "s1"), {"st": state})
+        want1 = {k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in state.items()}
+        assert take_plan_cache.hits == h0
+        for v in state.values():
+            if isinstance(v, torch.Tensor):
+                v.add_(1.0)  # training goes on: same tensors, new values
+        state["n"] = 4
+        s2 = Snapshot.take(str(tmp_path / "s2"), {"st": state})
+        assert take_plan_cache.hits == h0 + 1
+        want2 = {k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in state.items()}
+        m1, m2 = s1.get_manifest(), s2.get_manifest()
+        assert {k: (e.location, e.byte_range) for k, e in m1.items() if hasattr(e, "byte_range")} == {
+            k: (e.location, e.byte_range) for k, e in m2.items() if hasattr(e, "byte_range")}
+        check(s1, want1)
+        check(s2, want2)
+        # the on-disk metadata of the second snapshot is what a fresh process reads
+        check(Snapshot(str(tmp_path / "s2")), want2)
+        state["t7"] = torch.randn(121, 5, device="cuda", generator=g)  # replaced: another address
+        s3 = Snapshot.take(str(tmp_path / "s3"), {"st": state})
+        assert take_plan_cache.hits == h0 + 1
+        check(s3, dict(state))
+        state["t9"] = state["t9"].view(-1)  # same memory, another shape
+        s4 = Snapshot.take(str(tmp_path / "s4"), {"st": state})
+        assert take_plan_cache.hits == h0 + 1 and s4.get_manifest()["0/st/t9"].shape == [127 * 5]
+        check(s4, dict(state))
+        s5 = Snapshot.take(str(tmp_path / "s5"), {"st": state})
+        assert take_plan_cache.hits == h0 + 2
+        check(s5, dict(state))
+
+
 def test_async_take_is_consistent_under_mutation(tmp_path):
     g = torch.Generator(device="cuda").manual_seed(1)
     state = StateDict({f"t{i}": torch.randn(1 << 18, device="cuda", generator=g) for i in range(40)})

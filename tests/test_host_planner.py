@@ -466,3 +466,50 @@ def test_bulk_read_planner_gives_the_per_entry_reads():
         got = rr.buffer_consumer.unpack_region_array(base)
         assert sorted(map(bytes, got)) == sorted(map(bytes, want))
         assert rr.buffer_consumer.consumed_nbytes() == rr.byte_range[1] - rr.byte_range[0]
+
+
+def test_take_plan_cache_hits_only_on_identical_tensors():
+    """The plan of the previous take is reused when, and only when, every tensor is where it was, as it was."""
+    from torchsnapshot_b200.batcher import TakePlanCache, plan_cuda_tensors
+
+    def plan(tensors):
+        paths = list(tensors)
+        ts = [tensors[p] for p in paths]
+        return paths, ts, plan_cuda_tensors(paths, ts, ["0/" + p for p in paths], [False] * len(paths), 4096)
+
+    base = {f"t{i}": torch.zeros(10 + i, 3) for i in range(40)}
+    base["view"] = torch.zeros(50, 8)[:, ::2]
+    base["big"] = torch.zeros(5000)
+    cache = TakePlanCache()
+    paths, ts, (entries, wrs) = plan(base)
+    cfg = ("cfg",)
+    assert cache.get(cfg, paths, ts) is None
+    cache.put(cfg, paths, ts, entries, wrs)
+    # the same tensors through fresh Python objects (what module.state_dict() returns: detach() aliases)
+    again = [t.detach() for t in ts]
+    hit = cache.get(cfg, paths, again)
+    assert hit is not None and hit[0] is entries and hit[1] is wrs
+    slab_stagers = [w.buffer_stager for w in wrs if w.path.startswith("batched/")]
+    assert all(any(t is a for a in again) for st in slab_stagers for t in st.tensors), "the stagers hold the new aliases"
+    solo = [w.buffer_stager for w in wrs if not w.path.startswith("batched/")]
+    assert solo and all(any(st.tensor is a for a in again) for st in solo)
+    # anything different: no hit
+    assert cache.get(("other",), paths, again) is None
+    assert cache.get(cfg, paths[:-1], again[:-1]) is None
+    moved = list(again)
+    moved[3] = torch.zeros_like(moved[3])  # same shape, another address
+    assert cache.get(cfg, paths, moved) is None
+    reshaped = list(again)
+    reshaped[5] = reshaped[5].view(-1)  # same address and bytes, another shape
+    assert cache.get(cfg, paths, reshaped) is None
+    restrided = list(again)
+    i = paths.index("view")
+    restrided[i] = torch.zeros(50, 8)[:, ::2]
+    assert cache.get(cfg, paths, restrided) is None  # another base tensor
+    other_stride = list(again)
+    other_stride[i] = again[i].as_strided(again[i].shape, (4, 1))  # same address and shape, other strides
+    assert cache.get(cfg, paths, other_stride) is None
+    retyped = list(again)
+    retyped[7] = retyped[7].view(torch.int32)
+    assert cache.get(cfg, paths, retyped) is None
+    assert cache.get(cfg, paths, again) is not None

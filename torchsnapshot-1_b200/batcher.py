@@ -13,6 +13,8 @@ import itertools
 import os
 import threading
 import uuid
+
+import numpy as np
 from collections import defaultdict
 from concurrent.futures import Executor
 from enum import Enum
@@ -235,6 +237,15 @@ class GPUSlabStager(BufferStager):
         self.tensors = tensors  # keeps the members alive until the slab has been packed
         self._ptrs, self._offsets, self._nbytes, self._contiguous = ptrs, offsets, nbytes, contiguous
         self.slab_sz_bytes = size
+        self._dense = contiguous & (nbytes > 0)
+        # regions of the non-contiguous members, destination relative to the slab's first byte (a table of its
+        # own, so that packing needs no tensor object: only addresses and strides, read here once)
+        from .regions import pack_regions, regions_to_array
+
+        regs: List[RegionTuple] = []
+        for i in np.flatnonzero(~contiguous):
+            regs += pack_regions(tensors[int(i)], int(offsets[i]))
+        self._strided = regions_to_array(regs) if regs else None
 
     def is_device_stageable(self) -> bool:
         return True
@@ -244,21 +255,15 @@ class GPUSlabStager(BufferStager):
 
     def pack_region_array(self, dst_addr: int) -> Any:
         """The slab's pack regions as a REGION_DTYPE array (members back to back at dst_addr)."""
-        import numpy as np
-
-        from .regions import pack_regions, regions_to_array
-
-        dense = self._contiguous & (self._nbytes > 0)
+        dense = self._dense
         arr = np.zeros(int(dense.sum()), dtype=_native.REGION_DTYPE)
         arr["src"] = self._ptrs[dense]
         arr["dst"] = self._offsets[dense].astype(np.uint64) + np.uint64(dst_addr)
         arr["run_bytes"] = self._nbytes[dense].astype(np.uint64)
-        strided = np.flatnonzero(~self._contiguous)
-        if strided.size:
-            regs: List[RegionTuple] = []
-            for i in strided:
-                regs += pack_regions(self.tensors[int(i)], dst_addr + int(self._offsets[i]))
-            arr = np.concatenate([arr, regions_to_array(regs)])
+        if self._strided is not None:
+            tail = self._strided.copy()
+            tail["dst"] += np.uint64(dst_addr)
+            arr = np.concatenate([arr, tail])
         return arr
 
     def pack_regions(self, dst_addr: int) -> List[RegionTuple]:
@@ -354,6 +359,94 @@ def plan_cuda_tensors(
             start = stop
     # entries in the order the tensors were given (the manifest keeps insertion order)
     return {p: entries[p] for p in paths if p in entries}, write_reqs
+
+
+class TakePlanCache:
+    """The last bulk plan of a process, reused by the next take of the same tensors.
+
+    A training loop checkpoints the same state dict over and over: same paths, same tensors at the same
+    addresses with the same shapes.  Validating that (addresses, sizes, strides of the non-contiguous members,
+    dtypes, devices -- read through C-level iterators) costs less than half of planning again, and a take of
+    13 k tensors is mostly planning.  On a hit the entries and slab stagers of the previous plan are used as they
+    are: the manifest gets the same TensorEntry objects (they are never mutated after planning) and the slab
+    files the same `batched/<uuid>` names, inside the new snapshot's own directory.  Any difference -- one
+    address, one shape, a knob -- and the plan is made afresh.  TSB200_PLAN_CACHE=0 turns the cache off.
+
+    The cached stagers refer to the tensors of the LATEST take only (a hit swaps them in), so nothing older
+    than what the caller just checkpointed is kept alive."""
+
+    def __init__(self) -> None:
+        self.key: Any = None
+        self.value: Any = None
+        self.hits = 0
+        self.misses = 0
+
+    @staticmethod
+    def enabled() -> bool:
+        return os.environ.get("TSB200_PLAN_CACHE", "1").lower() not in ("0", "false")
+
+    @staticmethod
+    def fingerprint(tensors: List[Any]) -> Tuple[Any, ...]:
+        T = torch.Tensor
+        n = len(tensors)
+        contiguous = np.fromiter(map(T.is_contiguous, tensors), dtype=np.bool_, count=n)
+        return (
+            np.fromiter(map(T.data_ptr, tensors), dtype=np.uint64, count=n),
+            list(map(T.size, tensors)),
+            contiguous,
+            [tensors[int(i)].stride() for i in np.flatnonzero(~contiguous)],
+            [t.dtype for t in tensors],
+            np.fromiter(map(T.get_device, tensors), dtype=np.int64, count=n),
+        )
+
+    @staticmethod
+    def _same(a: Tuple[Any, ...], b: Tuple[Any, ...]) -> bool:
+        return (
+            len(a[1]) == len(b[1])
+            and np.array_equal(a[0], b[0])
+            and a[1] == b[1]
+            and np.array_equal(a[2], b[2])
+            and a[3] == b[3]
+            and a[4] == b[4]
+            and np.array_equal(a[5], b[5])
+        )
+
+    def get(self, config: Any, paths: List[str], tensors: List[Any]) -> Optional[Tuple[Dict[str, Any], List[WriteReq]]]:
+        if self.key is None or not self.enabled():
+            return None
+        cfg, cached_paths, fp = self.key
+        if cfg != config or cached_paths != paths or not self._same(fp, self.fingerprint(tensors)):
+            self.misses += 1
+            return None
+        self.hits += 1
+        entries, write_reqs, members = self.value
+        # the stagers keep THIS take's tensors alive from here on
+        for wr, idx in zip(write_reqs, members):
+            stager = wr.buffer_stager
+            if isinstance(stager, GPUSlabStager):
+                stager.tensors = [tensors[i] for i in idx]
+            else:
+                stager.tensor = tensors[idx[0]]
+        return entries, write_reqs
+
+    def put(self, config: Any, paths: List[str], tensors: List[Any], entries: Dict[str, Any],
+            write_reqs: List[WriteReq]) -> None:
+        if not self.enabled():
+            return
+        index = {id(t): i for i, t in enumerate(tensors)}
+        members = []
+        for wr in write_reqs:
+            stager = wr.buffer_stager
+            ts = stager.tensors if isinstance(stager, GPUSlabStager) else [stager.tensor]
+            members.append([index[id(t)] for t in ts])
+        self.key = (config, list(paths), self.fingerprint(tensors))
+        self.value = (entries, write_reqs, members)
+        from .manifest import register_stable_entries
+
+        register_stable_entries(entries.values())  # the metadata writer serialises these once
+
+
+take_plan_cache = TakePlanCache()
 
 
 class GPUSlabConsumer(BufferConsumer):

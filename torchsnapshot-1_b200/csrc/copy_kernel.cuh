@@ -363,7 +363,7 @@ template <typename T>
 __device__ __forceinline__ void copy_units(const TsbRegion* __restrict__ r, uint64_t src, uint64_t dst, uint32_t ndim,
                                            uint64_t first_unit, uint64_t nunits, uint32_t units_per_run,
                                            uint32_t tid, bool hint64) {
-  constexpr int U = sizeof(T) >= 16 ? 2 : 4;  // 32-64 bytes in flight per thread either way
+  constexpr int U = 4;
   for (uint64_t base = 0; base < nunits; base += (uint64_t)U * TSB_STRIDED_THREADS) {
     T v[U];
     T* dp[U];
@@ -507,16 +507,35 @@ __device__ __forceinline__ void transpose_tile(const TsbRegion* __restrict__ r, 
   const uint32_t wJ = (uint32_t)(nJ - j0 < TILE ? nJ - j0 : TILE), wL = (uint32_t)(nL - l0 < TILE ? nL - l0 : TILE);
   const unsigned char* sp = reinterpret_cast<const unsigned char*>(src + so) + j0 * sizeof(T) + (int64_t)l0 * sL;
   unsigned char* dp = reinterpret_cast<unsigned char*>(dst + dofs) + (int64_t)j0 * dJ + l0 * sizeof(T);
-  // in: consecutive threads along J (the source's contiguous dimension)
-  for (uint32_t i = tid; i < TILE * TILE; i += TSB_TRANSPOSE_THREADS) {
-    const uint32_t l = i / TILE, j = i % TILE;
-    if (j < wJ && l < wL) tile[l][j] = *reinterpret_cast<const T*>(sp + (uint64_t)j * sizeof(T) + (int64_t)l * sL);
+  constexpr int ROWS = TSB_TRANSPOSE_THREADS / TILE;  // tile rows one pass of the CTA covers
+  constexpr int PASSES = TILE / ROWS;
+  const uint32_t c = tid % TILE, r0 = tid / TILE;  // this thread's column, and its row in pass 0
+  if (wJ == TILE && wL == TILE) {
+    // full tile: every load of the thread is in flight before its first shared-memory store
+    T v[PASSES];
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p)
+      v[p] = *reinterpret_cast<const T*>(sp + (uint64_t)c * sizeof(T) + (int64_t)(r0 + p * ROWS) * sL);
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) tile[r0 + p * ROWS][c] = v[p];
+    __syncthreads();
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) v[p] = tile[c][r0 + p * ROWS];
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p)
+      *reinterpret_cast<T*>(dp + (int64_t)(r0 + p * ROWS) * dJ + (uint64_t)c * sizeof(T)) = v[p];
+    return;
+  }
+  // edge tile.  In: consecutive threads along J (the source's contiguous dimension) ...
+  for (int p = 0; p < PASSES; ++p) {
+    const uint32_t l = r0 + p * ROWS;
+    if (c < wJ && l < wL) tile[l][c] = *reinterpret_cast<const T*>(sp + (uint64_t)c * sizeof(T) + (int64_t)l * sL);
   }
   __syncthreads();
-  // out: consecutive threads along L (the destination's contiguous dimension)
-  for (uint32_t i = tid; i < TILE * TILE; i += TSB_TRANSPOSE_THREADS) {
-    const uint32_t j = i / TILE, l = i % TILE;
-    if (j < wJ && l < wL) *reinterpret_cast<T*>(dp + (int64_t)j * dJ + (uint64_t)l * sizeof(T)) = tile[l][j];
+  // ... out: consecutive threads along L (the destination's contiguous dimension)
+  for (int p = 0; p < PASSES; ++p) {
+    const uint32_t j = r0 + p * ROWS;
+    if (j < wJ && c < wL) *reinterpret_cast<T*>(dp + (int64_t)j * dJ + (uint64_t)c * sizeof(T)) = tile[c][j];
   }
 }
 

@@ -218,10 +218,28 @@ def _shards_text(shards: List["Shard"], pad: str) -> str:
     return "[\n" + ",\n".join(p + it for it in items) + "\n" + pad + "]"
 
 
+# Entries that are known not to change any more (batcher.TakePlanCache registers the entries of a cached plan,
+# which successive snapshots of one training job share): their text is produced once.  id -> (entry, text);
+# the entry is held so that the id cannot be reused by another object.
+_stable_text: Dict[int, Any] = {}
+
+
+def register_stable_entries(entries: Any) -> None:
+    """Replace the set of entries whose serialised text may be memoised (top-level manifest entries only)."""
+    _stable_text.clear()
+    for e in entries:
+        _stable_text[id(e)] = [e, None]
+
+
 def _entry_text(entry: Entry, pad: str) -> str:
     kind = type(entry)
     if kind is TensorEntry:
-        return _tensor_text(entry, pad)
+        memo = _stable_text.get(id(entry)) if pad == "    " else None
+        if memo is None:
+            return _tensor_text(entry, pad)
+        if memo[1] is None:
+            memo[1] = _tensor_text(entry, pad)
+        return memo[1]
     p = pad + "  "
     if kind is ShardedTensorEntry:
         return "{\n" f'{p}"type": "ShardedTensor",\n{p}"shards": {_shards_text(entry.shards, p)}\n{pad}}}'

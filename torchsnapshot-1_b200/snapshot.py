@@ -327,16 +327,24 @@ class Snapshot:
             if bulk:
                 from .batcher import plan_cuda_tensors
 
-                own = f"{rank}/"
-                if replicated_paths:
-                    flags = [p in replicated_paths for p in bulk]
-                    storage_paths = [("replicated/" if r else own) + p for p, r in zip(bulk, flags)]
+                from .batcher import take_plan_cache
+
+                tensors = [flattened[p] for p in bulk]
+                flags = [p in replicated_paths for p in bulk] if replicated_paths else None
+                config = (rank, world, is_async, max_chunk, knobs.get_slab_size_threshold_bytes(),
+                          tuple(flags) if flags is not None else None)
+                hit = take_plan_cache.get(config, bulk, tensors)
+                if hit is not None:
+                    bulk_entries, wrs = hit
                 else:
-                    flags = [False] * len(bulk)
-                    storage_paths = [own + p for p in bulk]
-                bulk_entries, wrs = plan_cuda_tensors(
-                    bulk, [flattened[p] for p in bulk], storage_paths, flags, None, is_async, max_chunk
-                )
+                    own = f"{rank}/"
+                    if flags is not None:
+                        storage_paths = [("replicated/" if r else own) + p for p, r in zip(bulk, flags)]
+                    else:
+                        flags = [False] * len(bulk)
+                        storage_paths = [own + p for p in bulk]
+                    bulk_entries, wrs = plan_cuda_tensors(bulk, tensors, storage_paths, flags, None, is_async, max_chunk)
+                    take_plan_cache.put(config, bulk, tensors, bulk_entries, wrs)
                 bulk_write_reqs.extend(wrs)
             for logical_path, obj in flattened.items():
                 if logical_path in bulk_entries:
