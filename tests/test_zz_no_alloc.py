@@ -6,7 +6,9 @@ device-wide synchronisation an allocation implies.  For them the library carries
 that works out of a fixed 2 MiB array inside the library instead of the context's arenas.  This test
 drives it through the C-ABI and holds its output to the output of the regular entry point
 (tsb_copy_regions) on the same regions, byte for byte, on two calls in a row -- the second one with a
-different, smaller job, so anything the first call left behind in the shared array would show.
+different, smaller job, so anything the first call left behind in the shared array would show -- and to
+the bytes the CPU oracle computes from host copies of the same tensors (two CUDA paths that agree could
+still both be wrong).
 
 The file name sorts last on purpose: a run that stops at the first failure has then already run every
 other test.  It also has to pass on its own in a fresh process, where its first call performs the
@@ -18,6 +20,7 @@ import pytest
 import torch
 
 import _cases
+import oracle
 from torchsnapshot_b200 import _native
 from torchsnapshot_b200.regions import box_regions, pack_regions, regions_to_array
 
@@ -78,6 +81,33 @@ def test_static_scratch_copy_matches_regular_entry_point(engine):
         torch.cuda.synchronize()
         assert torch.equal(got, want)  # bytes: no tolerance
         assert int(want[:shift].sum()) == 0x3C * shift and int(want[total:].sum()) == 0x3C * 32
+        # and both are what the reference's serialisation of the same tensors gives, member after member
+        expect = b"\x3c" * shift + b"".join(oracle.serialize(t.cpu()) for t in members) + b"\x3c" * 32
+        assert got.cpu().numpy().tobytes() == expect
+
+
+def test_static_scratch_copy_is_refused_on_a_capturing_stream(engine):
+    """The descriptor upload reads a host buffer the next call overwrites, so the call must not end up inside a
+    CUDA graph: on a stream that is being captured it is refused, nothing is enqueued, and the capture goes on."""
+    device = engine.device
+    src = torch.arange(4096, dtype=torch.uint8, device=f"cuda:{device}")
+    dst = torch.zeros(4096, dtype=torch.uint8, device=f"cuda:{device}")
+    arr = regions_to_array([(src.data_ptr(), dst.data_ptr(), 4096, (), (), ())])
+    _native.copy_regions_static(device, torch.cuda.current_stream().cuda_stream, arr)  # set-up call, outside any capture
+    torch.cuda.synchronize()
+    assert torch.equal(dst, src)
+    dst.zero_()
+    side = torch.cuda.Stream(device=device)
+    graph = torch.cuda.CUDAGraph()
+    x = torch.zeros(8, device=f"cuda:{device}")
+    torch.cuda.synchronize()
+    with torch.cuda.graph(graph, stream=side):
+        x += 1
+        with pytest.raises(_native.TsbError, match="captured"):
+            _native.copy_regions_static(device, side.cuda_stream, arr)
+    graph.replay()
+    torch.cuda.synchronize()
+    assert int(dst.sum()) == 0 and float(x.sum()) == 8.0
 
 
 def test_static_scratch_limits_are_refused_before_any_work(engine):

@@ -262,7 +262,7 @@ __device__ __forceinline__ void copy_vec_shifted(uint4* __restrict__ d4, const u
   }
 }
 
-// Cooperative byte-exact copy of n bytes by a group of NL threads (lane in [0, NL)); NL = 8, 16 or 32.
+// Cooperative byte-exact copy of n bytes by a group of NL threads (lane in [0, NL)); NL = 4, 8, 16 or 32.
 template <int NL>
 __device__ __forceinline__ void copy_span(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint64_t n,
                                           uint32_t lane) {
@@ -434,7 +434,7 @@ tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __
   // 2.65 / 4.0-4.4 TB/s with 1 / 2 / 4 / 8-byte units whatever the run length, one-run-per-warp moves 0.75 /
   // 1.42 / 2.48 / 3.99 / 4.24 / 6.34 TB/s for runs of 64 / 128 / 256 / 512 / 1024 / 4096 bytes -- so the
   // warp form wins from 128 x unit bytes on.
-  // (r02) The group that takes a run is as wide as the run is long: 8 lanes up to 128 bytes, 16 up to 256, a whole
+  // (r02) The group that takes a run is as wide as the run is long: 4 lanes up to 64 bytes, 8 up to 128, 16 up to 256, a whole
   // warp above -- a warp per 64-byte run left 28 lanes idle (0.75 TB/s).  With groups, runs misaligned by 1, 2
   // or 4 bytes take this form from 48 bytes on instead of crawling unit by unit (0.79 / 1.45 / 2.65 TB/s);
   // 8-byte-aligned runs keep the unit form (4.0-4.4 TB/s) until the run form overtakes it (`warp_run_min` units).
@@ -444,7 +444,9 @@ tsb_copy_strided_kernel(const TsbRegion* __restrict__ regions, const TsbTile* __
     // the host emits whole runs per tile for this class
     const uint64_t q0 = off / run_bytes;
     const uint32_t nruns = len / (uint32_t)run_bytes;
-    if (run_bytes <= 128u) {
+    if (run_bytes <= 64u) {
+      strided_runs<4>(r, src, dst, ndim, q0, nruns, run_bytes, tid);
+    } else if (run_bytes <= 128u) {
       strided_runs<8>(r, src, dst, ndim, q0, nruns, run_bytes, tid);
     } else if (run_bytes <= 256u) {
       strided_runs<16>(r, src, dst, ndim, q0, nruns, run_bytes, tid);
