@@ -380,6 +380,24 @@ class TakePlanCache:
         self.value: Any = None
         self.hits = 0
         self.misses = 0
+        self._columns: Any = None  # wire form of the cached entries (manifest.tensor_columns_of), made on first use
+
+    def columns_for(self, manifest: Dict[str, Any]) -> Any:
+        """Pre-encoded columns of the cached plan's entries when `manifest` carries exactly those objects (the
+        take that is being planned hit, or just filled, the cache); else None."""
+        if self.value is None or not self.enabled():
+            return None
+        entries = self.value[0]
+        if not entries:
+            return None
+        first = next(iter(entries))
+        if manifest.get(first) is not entries[first]:
+            return None
+        if self._columns is None or self._columns[0] is not entries:
+            from .manifest import tensor_columns_of
+
+            self._columns = tensor_columns_of(entries)
+        return self._columns
 
     @staticmethod
     def enabled() -> bool:

@@ -340,6 +340,100 @@ class SnapshotMetadata:
         return cls(version=doc["version"], world_size=doc["world_size"], manifest=manifest)
 
 
+# ------------------------------------------------------------------------------------------------
+# compact wire form of a rank's manifest (the take-side all-gather, reference snapshot.py:352-358)
+# ------------------------------------------------------------------------------------------------
+# The reference gathers every rank's manifest as pickled entry objects; with 13 k tensors per rank that is most
+# of the time an 8-rank job is blocked in async_take (each rank unpickles 100 k dataclass instances).  Here a
+# rank sends its TensorEntry objects -- practically all of a manifest -- as columns of strings and ints, which
+# pickle an order of magnitude faster, and a receiver only rebuilds entries when somebody asks for them
+# (`SnapshotMetadata.lazy`): rank 0 in the thread that writes the metadata file, the others not at all unless
+# the snapshot object is used to restore.
+def encode_manifest(manifest: Manifest, tensor_columns: Optional[Any] = None) -> bytes:
+    """`manifest` as bytes.  `tensor_columns` = (entries dict, pickled columns) from an earlier call with the SAME
+    TensorEntry objects (see `tensor_columns_of`) skips re-encoding them; they then come last in the decoded
+    manifest."""
+    import pickle
+
+    cached: Dict[str, Any] = tensor_columns[0] if tensor_columns is not None else {}
+    paths, locations, serializers, dtypes, shapes, replicated, ranges, others = [], [], [], [], [], [], [], []
+    for path, e in manifest.items():
+        if type(e) is TensorEntry:
+            if cached and cached.get(path) is e:
+                continue
+            paths.append(path)
+            locations.append(e.location)
+            serializers.append(e.serializer)
+            dtypes.append(e.dtype)
+            shapes.append(e.shape)
+            replicated.append(e.replicated)
+            ranges.append(e.byte_range)
+        else:
+            others.append((len(paths), path, e))  # position among the tensor entries, to restore the order
+    head = pickle.dumps((paths, locations, serializers, dtypes, shapes, replicated, ranges, others), protocol=5)
+    return pickle.dumps((head, tensor_columns[1] if tensor_columns is not None else None), protocol=5)
+
+
+def tensor_columns_of(entries: Dict[str, Any]) -> Any:
+    """Pre-encoded columns of a dict of TensorEntry objects that will be sent unchanged take after take."""
+    import pickle
+
+    vals = list(entries.values())
+    blob = pickle.dumps((list(entries.keys()), [e.location for e in vals], [e.serializer for e in vals],
+                         [e.dtype for e in vals], [e.shape for e in vals], [e.replicated for e in vals],
+                         [e.byte_range for e in vals], []), protocol=5)
+    return (entries, blob)
+
+
+def _decode_columns(blob: bytes, out: Manifest) -> None:
+    import pickle
+
+    paths, locations, serializers, dtypes, shapes, replicated, ranges, others = pickle.loads(blob)
+    new, cls = object.__new__, TensorEntry
+    k = 0
+    for i, path in enumerate(paths):
+        while k < len(others) and others[k][0] <= i:
+            out[others[k][1]] = others[k][2]
+            k += 1
+        e = new(cls)
+        e.__dict__ = {"type": "Tensor", "location": locations[i], "serializer": serializers[i], "dtype": dtypes[i],
+                      "shape": shapes[i], "replicated": replicated[i], "byte_range": ranges[i]}
+        out[path] = e
+    for _pos, path, e in others[k:]:
+        out[path] = e
+
+
+def decode_manifest(blob: bytes) -> Manifest:
+    import pickle
+
+    head, tail = pickle.loads(blob)
+    out: Manifest = {}
+    _decode_columns(head, out)
+    if tail is not None:
+        _decode_columns(tail, out)
+    return out
+
+
+class LazySnapshotMetadata(SnapshotMetadata):
+    """SnapshotMetadata whose manifest is rebuilt from the ranks' encoded manifests on first use."""
+
+    def __init__(self, version: str, world_size: int, parts: List[Any]) -> None:
+        self.version = version
+        self.world_size = world_size
+        self._parts = parts  # per rank: its manifest as a dict, or encoded (`encode_manifest`)
+
+    def __getattr__(self, name: str) -> Any:
+        if name == "manifest":
+            manifest: Manifest = {}
+            for rank, part in enumerate(self.__dict__["_parts"]):
+                prefix = f"{rank}/"
+                for path, entry in (decode_manifest(part) if isinstance(part, bytes) else part).items():
+                    manifest[prefix + path] = entry
+            self.manifest = manifest
+            return manifest
+        raise AttributeError(name)
+
+
 def is_dict_entry(entry: Any) -> bool:
     return getattr(entry, "type", None) in ("dict", "OrderedDict")
 

@@ -58,29 +58,29 @@ def assign_write_loads(
         # profiles/r01_peaks_n8.txt)
         speed = [min(max(s / mean, 0.25), 4.0) for s in rank_to_speed]
 
-    def lightest() -> int:
-        return min(range(len(sizes)), key=lambda r: (sizes[r] / speed[r], r))
-
+    # finish time of every rank so far; the lightest rank is the first minimum (ties go to the lower rank)
+    finish = [sizes[r] / speed[r] for r in range(len(sizes))]
+    cost = [1.0 / x for x in speed]
     # whole logical paths first, then the chunks of sub-partitionable paths (reference order)
-    grouped: Dict[str, List[Tuple[int, int]]] = defaultdict(list)
-    order: List[str] = []
+    grouped: Dict[str, List[Tuple[int, int]]] = {}
     chunk_units: List[Tuple[str, int, int]] = []
     for path, idx, size, sub in loads:
         if sub:
             chunk_units.append((path, idx, size))
-            continue
-        if path not in grouped:
-            order.append(path)
-        grouped[path].append((idx, size))
-    for path in order:
-        r = lightest()
-        for idx, size in grouped[path]:
-            out[r].append((path, idx))
-            sizes[r] += size
+        elif path in grouped:
+            grouped[path].append((idx, size))
+        else:
+            grouped[path] = [(idx, size)]
+    for path, members in grouped.items():
+        r = finish.index(min(finish))
+        mine = out[r]
+        for idx, size in members:
+            mine.append((path, idx))
+            finish[r] += size * cost[r]
     for path, idx, size in chunk_units:
-        r = lightest()
+        r = finish.index(min(finish))
         out[r].append((path, idx))
-        sizes[r] += size
+        finish[r] += size * cost[r]
     return out
 
 
@@ -161,13 +161,11 @@ class RanksDisagree(RuntimeError):
 
 
 def _digest(parts: Any) -> str:
+    """Digest of a list of strings / tuples of strings and ints that is the same in every process (`hash()` of a
+    str is not)."""
     import hashlib
 
-    h = hashlib.blake2b(digest_size=12)
-    for part in parts:
-        h.update(str(part).encode("utf-8"))
-        h.update(b"\n")
-    return h.hexdigest()
+    return hashlib.blake2b(repr(parts).encode("utf-8"), digest_size=12).hexdigest()
 
 
 def partition_write_reqs(

@@ -42,6 +42,9 @@ from .manifest import (
     ShardedTensorEntry,
     SnapshotMetadata,
     TensorEntry,
+    LazySnapshotMetadata,
+    decode_manifest,
+    encode_manifest,
     is_container_entry,
     is_replicated,
 )
@@ -331,7 +334,8 @@ class Snapshot:
 
                 tensors = [flattened[p] for p in bulk]
                 flags = [p in replicated_paths for p in bulk] if replicated_paths else None
-                config = (rank, world, is_async, max_chunk, knobs.get_slab_size_threshold_bytes(),
+                # (sync / async is not part of the key: it only matters to CPU tensors, which are not planned here)
+                config = (rank, world, max_chunk, knobs.get_slab_size_threshold_bytes(),
                           tuple(flags) if flags is not None else None)
                 hit = take_plan_cache.get(config, bulk, tensors)
                 if hit is not None:
@@ -398,15 +402,30 @@ class Snapshot:
         mark("batch")
 
         # ---- collective 3: the manifest ----------------------------------------------------------
-        manifests: List[Any] = [None] * world
-        pg.all_gather_object(manifests, manifest)
-        if world > 1:  # with one rank every replicated entry already sits under rank 0
-            manifests = consolidate_replicated_entries(manifests)
-        global_manifest: Manifest = {}
-        for r, m in enumerate(manifests):
-            prefix = f"{r}/"
-            for logical_path, entry in m.items():
-                global_manifest[prefix + logical_path] = entry
+        # Every rank's entries travel as columns of strings and ints (manifest.encode_manifest), and nobody
+        # rebuilds other ranks' entries before somebody needs them -- rank 0 in the thread that writes the
+        # metadata file, after async_take has returned.  Only replicated entries have to be looked at right
+        # away: they are merged and listed once, under rank 0 (partitioner.consolidate_replicated_entries).
+        metadata: SnapshotMetadata
+        if world == 1:  # with one rank every replicated entry already sits under rank 0
+            metadata = LazySnapshotMetadata(VERSION, 1, [manifest])
+        else:
+            from .batcher import take_plan_cache
+
+            parts: List[Any] = [None] * world
+            pg.all_gather_object(
+                parts, (bool(replicated_paths), encode_manifest(manifest, take_plan_cache.columns_for(manifest)))
+            )
+            if any(flag for flag, _blob in parts):
+                manifests = consolidate_replicated_entries([decode_manifest(blob) for _flag, blob in parts])
+                global_manifest: Manifest = {}
+                for r, m in enumerate(manifests):
+                    prefix = f"{r}/"
+                    for logical_path, entry in m.items():
+                        global_manifest[prefix + logical_path] = entry
+                metadata = SnapshotMetadata(version=VERSION, world_size=world, manifest=global_manifest)
+            else:
+                metadata = LazySnapshotMetadata(VERSION, world, [blob for _flag, blob in parts])
         mark("manifest_gather")
 
         pending = sync_execute_write_reqs(
@@ -419,7 +438,6 @@ class Snapshot:
         mark("stage")
         global last_take_phases
         last_take_phases = phases
-        metadata = SnapshotMetadata(version=VERSION, world_size=world, manifest=global_manifest)
         return path, pending, metadata, storage
 
     # ------------------------------------------------------------------------------------------
