@@ -131,6 +131,13 @@ int tsb_dev_alloc_exportable(TsbCtx* ctx, uint64_t nbytes, uint64_t* dptr);
  * memoryview of, io_types.py:19-26; the reference uses pageable memory, tensor.py:248-251).
  */
 int tsb_host_alloc(TsbCtx* ctx, uint64_t nbytes, void** hptr);
+/*
+ * The same, but only out of segments the arena already holds: TSB_EAGAIN instead of pinning new memory
+ * (first touch + cudaHostRegister cost ~40 ms per GiB).  For callers on a latency-critical thread -- the event
+ * loop of an async_take -- which then grow the arena from a worker thread with tsb_host_alloc.  No reference
+ * counterpart (the reference allocates pageable host memory per copy, tensor.py:248-254).
+ */
+int tsb_host_alloc_nogrow(TsbCtx* ctx, uint64_t nbytes, void** hptr);
 int tsb_host_free(TsbCtx* ctx, void* hptr);
 
 /* Bytes currently handed out / reserved from the driver, per arena (0 = host, 1 = device). */

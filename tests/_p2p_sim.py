@@ -149,7 +149,7 @@ class FakeEngine:
         self.device = rank
         self.launches = 0
 
-    def pinned(self, nbytes: int) -> FakePinned:
+    def pinned(self, nbytes: int, grow: bool = True) -> FakePinned:
         return FakePinned(nbytes)
 
     def wait_current_stream(self, stream: int) -> None:

@@ -60,6 +60,7 @@ _SIGNATURES = {
     "tsb_dev_alloc_exportable": (_i, [_p, _u64, ctypes.POINTER(_u64)]),
     "tsb_dev_free": (_i, [_p, _u64]),
     "tsb_host_alloc": (_i, [_p, _u64, ctypes.POINTER(_p)]),
+    "tsb_host_alloc_nogrow": (_i, [_p, _u64, ctypes.POINTER(_p)]),
     "tsb_host_free": (_i, [_p, _p]),
     "tsb_arena_stats": (_i, [_p, _i, ctypes.POINTER(_u64), ctypes.POINTER(_u64), ctypes.POINTER(_u64)]),
     "tsb_arena_trim": (_i, [_p]),
@@ -177,6 +178,12 @@ class Context:
     def host_alloc(self, nbytes: int) -> int:
         out = _p()
         _check(self.lib, self.lib.tsb_host_alloc(self._h, nbytes, ctypes.byref(out)))
+        return out.value or 0
+
+    def host_alloc_nogrow(self, nbytes: int) -> int:
+        """Pinned block out of the segments the arena already holds; ArenaFull if that takes new pinned memory."""
+        out = _p()
+        _check(self.lib, self.lib.tsb_host_alloc_nogrow(self._h, nbytes, ctypes.byref(out)))
         return out.value or 0
 
     def host_free(self, hptr: int) -> None:

@@ -60,11 +60,13 @@ class Arena {
   Arena(bool host, uint64_t bound, uint64_t seg_default, uint64_t align)
       : host_(host), bound_(bound), seg_default_(seg_default), align_(align) {}
 
-  int alloc(uint64_t nbytes, uint64_t* out) {
+  int alloc(uint64_t nbytes, uint64_t* out, bool may_grow = true) {
     if (nbytes == 0) nbytes = 1;
     const uint64_t need = (nbytes + align_ - 1) / align_ * align_;
     std::lock_guard<std::mutex> g(mu_);
     if (try_alloc(need, out)) return TSB_OK;
+    if (!may_grow) return set_err(TSB_EAGAIN, "%s arena: no free block of %llu bytes in the existing segments",
+                                  host_ ? "host" : "device", (unsigned long long)need);
     if (need > bound_)
       return set_err(TSB_ENOMEM, "%s arena: request of %llu bytes exceeds the arena bound of %llu bytes",
                      host_ ? "host" : "device", (unsigned long long)need, (unsigned long long)bound_);
@@ -540,7 +542,7 @@ static int build_tiles(const TsbRegion* regions, uint32_t n, TilePlan& plan) {
 // ------------------------------------------------------------------------------------------
 extern "C" {
 
-int tsb_version(void) { return 1001; }
+int tsb_version(void) { return 1002; }
 
 const char* tsb_last_error(void) { return g_err; }
 
@@ -699,6 +701,15 @@ int tsb_host_alloc(TsbCtx* ctx, uint64_t nbytes, void** hptr) {
     reap_scratch(ctx, false);
     rc = ctx->host_arena->alloc(nbytes, &a);
   }
+  *hptr = (void*)(uintptr_t)a;
+  return rc;
+}
+
+int tsb_host_alloc_nogrow(TsbCtx* ctx, uint64_t nbytes, void** hptr) {
+  CHECK_CTX(ctx);
+  if (!hptr) return set_err(TSB_EINVAL, "null argument");
+  uint64_t a = 0;
+  int rc = ctx->host_arena->alloc(nbytes, &a, false);
   *hptr = (void*)(uintptr_t)a;
   return rc;
 }

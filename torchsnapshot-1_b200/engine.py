@@ -33,10 +33,11 @@ class PinnedBuffer:
     when the reference's scheduler reclaims buffer memory (scheduler.py:87-90).
     """
 
-    def __init__(self, engine: "Engine", nbytes: int) -> None:
+    def __init__(self, engine: "Engine", nbytes: int, grow: bool = True) -> None:
         self.engine = engine
         self.nbytes = nbytes
-        self.ptr = engine.ctx.host_alloc(max(nbytes, 1))  # raises ArenaFull when at the bound
+        # raises ArenaFull when at the bound (or, with grow=False, when new memory would have to be pinned)
+        self.ptr = engine.ctx.host_alloc(max(nbytes, 1)) if grow else engine.ctx.host_alloc_nogrow(max(nbytes, 1))
         self._array = (ctypes.c_uint8 * nbytes).from_address(self.ptr)
         self._finalizer = weakref.finalize(self, engine.ctx.host_free, self.ptr)
 
@@ -97,8 +98,8 @@ class Engine:
             cur = torch.cuda.current_stream().cuda_stream
         self.ctx.external_wait_stream(cur, stream)
 
-    def pinned(self, nbytes: int) -> PinnedBuffer:
-        return PinnedBuffer(self, nbytes)
+    def pinned(self, nbytes: int, grow: bool = True) -> PinnedBuffer:
+        return PinnedBuffer(self, nbytes, grow)
 
     def host_in_use(self) -> int:
         return self.ctx.arena_stats(0)[0]

@@ -228,7 +228,12 @@ class _Allocator:
             over = self.budget is not None and self.pinned_inflight > 0 and self.pinned_inflight + nbytes > self.budget
             if not over:
                 try:
-                    buf = eng.pinned(nbytes)
+                    try:
+                        buf = eng.pinned(nbytes, False)  # out of the segments the arena already holds
+                    except ArenaFull:
+                        # Pinning new memory costs ~40 ms per GiB: never on the event-loop thread, where it
+                        # would hold up everything else -- the consistency point of an async_take included.
+                        buf = await asyncio.get_running_loop().run_in_executor(None, eng.pinned, nbytes)
                     self.outstanding += 1
                     self.pinned_inflight += nbytes
                     return buf
