@@ -78,6 +78,7 @@ def read_concurrency() -> int:
 
 
 _TRACE_READS = os.environ.get("TSB200_TRACE_READS") == "1"
+_TRACE_WRITES = os.environ.get("TSB200_TRACE_WRITES") == "1"
 _STAGING_ALIGN = 512  # each file's bytes start 512-B aligned inside the device staging block
 
 
@@ -145,6 +146,7 @@ class _Stats:
         # requests packed straight into pinned host memory (no device staging available): kernel events, bytes
         self.host_pack_events: List[Tuple[Engine, int, int, int]] = []
         self.host_packed_bytes = 0
+        self.write_trace: List[Tuple[float, float, float, int]] = []  # per file (TSB200_TRACE_WRITES=1): ready, start, end, bytes
 
     def kernel_ms(self) -> float:
         return sum(eng.ctx.event_elapsed_ms(a, b) for eng, a, b, _n in self.kernel_events)
@@ -355,9 +357,13 @@ async def execute_write_reqs(
 
     async def write_out(path: str, buf: BufferType, on_done: Any = None) -> None:
         try:
+            t_ready = time.monotonic()
             async with io_slots:
+                t_start = time.monotonic()
                 await storage.write(WriteIO(path=path, buf=buf))
             stats.bytes += len(buf)
+            if _TRACE_WRITES:
+                stats.write_trace.append((t_ready - stats.begin, t_start - stats.begin, time.monotonic() - stats.begin, len(buf)))
         finally:
             if isinstance(buf, memoryview):
                 try:
