@@ -36,6 +36,8 @@ class FSStoragePlugin(StoragePlugin):
         # TSB200_FS_DIRECT=1: page-cache bypass (O_DIRECT) for the aligned body of every transfer -- for real
         # block devices; tmpfs has no use for it
         self._flags = _native.FILE_DIRECT if knobs.is_fs_direct_enabled() else 0
+        if self._flags:
+            self.write_streamed = None  # type: ignore[assignment]  (O_DIRECT transfers want whole, aligned buffers)
 
     def _prepare(self, rel: str) -> str:
         path = os.path.join(self.root, rel)
@@ -68,6 +70,27 @@ class FSStoragePlugin(StoragePlugin):
     async def write(self, write_io: WriteIO) -> None:
         path = self._prepare(write_io.path)
         await asyncio.get_running_loop().run_in_executor(self._executor, self._write_sync, path, write_io.buf)
+
+    def _write_streamed_sync(self, path: str, buf: Any, wait_more: Any) -> None:
+        n = len(buf)
+        fd = os.open(path, os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o644)
+        try:
+            view = memoryview(buf)
+            done = 0
+            while done < n:
+                upto = wait_more(done)  # blocks until more of the buffer is valid
+                while done < upto:
+                    done += os.pwrite(fd, view[done:upto], done)
+        finally:
+            os.close(fd)
+
+    async def write_streamed(self, path: str, buf: Any, wait_more: Any) -> None:
+        """Optional extension next to the ABI (like `read_into`): write a buffer whose bytes become valid front to
+        back while the call runs.  `wait_more(done) -> upto` blocks until bytes beyond `done` are valid.  One
+        writer thread per file follows the device->host copies, so a file is on storage shortly after its
+        last byte has left the GPU.  Same file as `write` produces."""
+        full = self._prepare(path)
+        await asyncio.get_running_loop().run_in_executor(self._executor, self._write_streamed_sync, full, buf, wait_more)
 
     def _read_sync(self, path: str, byte_range: Optional[Tuple[int, int]], out: Optional[memoryview]) -> bytearray:
         if byte_range is None:
