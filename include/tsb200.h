@@ -238,6 +238,16 @@ int tsb_copy_regions_static(int device, uint64_t cuda_stream, const TsbRegion* r
 /* Device <-> pinned host copies on a context stream (K3 / K6). `hptr` should come from tsb_host_alloc. */
 int tsb_memcpy_d2h(TsbCtx* ctx, int stream, void* hptr, uint64_t dptr, uint64_t nbytes);
 int tsb_memcpy_h2d(TsbCtx* ctx, int stream, uint64_t dptr, const void* hptr, uint64_t nbytes);
+/*
+ * `n` device -> pinned host copies issued INTERLEAVED on one stream, `chunk` bytes at a time round-robin over
+ * the copies, with an event recorded after every chunk: events[] receives, copy after copy,
+ * ceil(nbytes[b] / chunk) handles (release each with tsb_event_release).  One call per batch of files, so that
+ * every file of the batch starts arriving at once and a writer can follow each of them
+ * (tsb_file_write_streamed).  Replaces one gpu_buf.cpu() per slab (batcher.py:156) / tensor.to("cpu") per
+ * large tensor (io_preparers/tensor.py:252-254), which finish one file before the next one starts.
+ */
+int tsb_memcpy_d2h_interleaved(TsbCtx* ctx, int stream, uint32_t n, const uint64_t* hptrs, const uint64_t* dptrs,
+                               const uint64_t* nbytes, uint64_t chunk, TsbEvent* events);
 /* Device -> device (same or peer device) on a context stream. */
 int tsb_memcpy_d2d(TsbCtx* ctx, int stream, uint64_t dst, uint64_t src, uint64_t nbytes);
 
@@ -282,6 +292,14 @@ int tsb_peer_enable(TsbCtx* ctx, int peer_device);
  * pwrite workers (0 = library default).  Replaces the aiofiles write of FSStoragePlugin.write
  * (storage_plugins/fs.py:26-36). */
 int tsb_file_write(const char* path, const void* hptr, uint64_t nbytes, int nthreads, uint32_t flags);
+/*
+ * Write a buffer that is still being filled: bytes [0, ends[i]) are valid once events[i] (in order) has
+ * completed.  The calling thread waits for each event in turn and writes what has arrived, so the file is
+ * complete shortly after the last copy.  Same file as tsb_file_write produces (FSStoragePlugin.write,
+ * fs.py:26-36, which needs the whole buffer before it starts).
+ */
+int tsb_file_write_streamed(TsbCtx* ctx, const char* path, const void* hptr, uint64_t nbytes, const TsbEvent* events,
+                            const uint64_t* ends, uint32_t n);
 /* Read `nbytes` at `offset` of `path` into `hptr` (FSStoragePlugin.read, fs.py:38-49). */
 int tsb_file_read(const char* path, uint64_t offset, void* hptr, uint64_t nbytes, int nthreads, uint32_t flags);
 

@@ -78,6 +78,8 @@ _SIGNATURES = {
     "tsb_copy_regions_static": (_i, [_i, _u64, _p, ctypes.c_uint32]),
     "tsb_memcpy_d2h": (_i, [_p, _i, _p, _u64, _u64]),
     "tsb_memcpy_h2d": (_i, [_p, _i, _u64, _p, _u64]),
+    "tsb_memcpy_d2h_interleaved": (_i, [_p, _i, ctypes.c_uint32, _p, _p, _p, _u64, _p]),
+    "tsb_file_write_streamed": (_i, [_p, ctypes.c_char_p, _p, _u64, _p, _p, ctypes.c_uint32]),
     "tsb_memcpy_d2d": (_i, [_p, _i, _u64, _u64, _u64]),
     "tsb_host_memcpy": (_i, [_p, _p, _u64, _i]),
     "tsb_host_gather": (_i, [_p, _p, _p, _u64, _i]),
@@ -257,6 +259,30 @@ class Context:
 
     def memcpy_d2h(self, stream: int, hptr: int, dptr: int, nbytes: int) -> None:
         _check(self.lib, self.lib.tsb_memcpy_d2h(self._h, stream, hptr, dptr, nbytes))
+
+    def memcpy_d2h_interleaved(self, stream: int, hptrs: Any, dptrs: Any, nbytes: Any, chunk: int) -> Any:
+        """Interleaved chunked D2H copies of several buffers; returns, per buffer, (event handles, end offsets) as
+        uint64 numpy arrays (one event per chunk; the caller releases them)."""
+        h = np.ascontiguousarray(hptrs, dtype=np.uint64)
+        d = np.ascontiguousarray(dptrs, dtype=np.uint64)
+        n = np.ascontiguousarray(nbytes, dtype=np.uint64)
+        counts = [(int(x) + chunk - 1) // chunk for x in n]
+        events = np.zeros(max(sum(counts), 1), dtype=np.uint64)
+        _check(self.lib, self.lib.tsb_memcpy_d2h_interleaved(self._h, stream, len(counts), h.ctypes.data, d.ctypes.data,
+                                                             n.ctypes.data, chunk, events.ctypes.data))
+        out, at = [], 0
+        for c, size in zip(counts, n):
+            ends = np.minimum(np.arange(1, c + 1, dtype=np.uint64) * np.uint64(chunk), size)
+            out.append((events[at : at + c].copy(), ends))
+            at += c
+        return out
+
+    def file_write_streamed(self, path: str, hptr: int, nbytes: int, events: Any, ends: Any) -> None:
+        """Write a pinned buffer while it is being filled (events[i] done => bytes [0, ends[i]) valid)."""
+        ev = np.ascontiguousarray(events, dtype=np.uint64)
+        en = np.ascontiguousarray(ends, dtype=np.uint64)
+        _check(self.lib, self.lib.tsb_file_write_streamed(self._h, os.fsencode(path), hptr, nbytes, ev.ctypes.data,
+                                                          en.ctypes.data, int(ev.shape[0])))
 
     def memcpy_h2d(self, stream: int, dptr: int, hptr: int, nbytes: int) -> None:
         _check(self.lib, self.lib.tsb_memcpy_h2d(self._h, stream, dptr, hptr, nbytes))

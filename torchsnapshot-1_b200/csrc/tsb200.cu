@@ -542,7 +542,7 @@ static int build_tiles(const TsbRegion* regions, uint32_t n, TilePlan& plan) {
 // ------------------------------------------------------------------------------------------
 extern "C" {
 
-int tsb_version(void) { return 1002; }
+int tsb_version(void) { return 1003; }
 
 const char* tsb_last_error(void) { return g_err; }
 
@@ -998,6 +998,53 @@ int tsb_memcpy_d2h(TsbCtx* ctx, int stream, void* hptr, uint64_t dptr, uint64_t 
   return TSB_OK;
 }
 
+int tsb_memcpy_d2h_interleaved(TsbCtx* ctx, int stream, uint32_t n, const uint64_t* hptrs, const uint64_t* dptrs,
+                               const uint64_t* nbytes, uint64_t chunk, TsbEvent* events) {
+  CHECK_CTX(ctx);
+  CHECK_STREAM(stream);
+  if (n == 0) return TSB_OK;
+  if (!hptrs || !dptrs || !nbytes || !events || chunk == 0) return set_err(TSB_EINVAL, "null argument");
+  std::vector<uint64_t> pos(n, 0), slot(n, 0);
+  uint64_t total = 0;
+  for (uint32_t b = 0; b < n; ++b) {
+    slot[b] = total;
+    total += (nbytes[b] + chunk - 1) / chunk;
+  }
+  uint64_t recorded = 0;
+  int rc = TSB_OK;
+  for (bool left = true; left && rc == TSB_OK;) {
+    left = false;
+    for (uint32_t b = 0; b < n && rc == TSB_OK; ++b) {
+      if (pos[b] >= nbytes[b]) continue;
+      const uint64_t c = std::min(chunk, nbytes[b] - pos[b]);
+      cudaError_t e = cudaMemcpyAsync((void*)(uintptr_t)(hptrs[b] + pos[b]), (const void*)(uintptr_t)(dptrs[b] + pos[b]), c,
+                                      cudaMemcpyDeviceToHost, ctx->streams[stream]);
+      if (e != cudaSuccess) {
+        rc = set_err(TSB_ECUDA, "cudaMemcpyAsync failed: %s", cudaGetErrorString(e));
+        break;
+      }
+      pos[b] += c;
+      rc = tsb_event_record(ctx, stream, &events[slot[b]++]);
+      if (rc == TSB_OK) ++recorded;
+      left = true;
+    }
+  }
+  if (rc != TSB_OK) {  // no handle survives a failed call
+    char keep[sizeof(g_err)];
+    memcpy(keep, g_err, sizeof(keep));
+    uint64_t base = 0;
+    for (uint32_t b = 0; b < n; ++b) {
+      const uint64_t cnt = (nbytes[b] + chunk - 1) / chunk;
+      for (uint64_t j = base; j < slot[b] && j < base + cnt; ++j)
+        if (events[j]) tsb_event_release(ctx, events[j]);
+      base += cnt;
+    }
+    memcpy(g_err, keep, sizeof(keep));
+  }
+  (void)recorded;
+  return rc;
+}
+
 int tsb_memcpy_h2d(TsbCtx* ctx, int stream, uint64_t dptr, const void* hptr, uint64_t nbytes) {
   CHECK_CTX(ctx);
   CHECK_STREAM(stream);
@@ -1313,6 +1360,44 @@ static int file_rw(const char* path, bool write, uint64_t offset, void* hptr, ui
   if (!err) err = rw_parallel(fd, write, (char*)hptr + direct_len, offset + direct_len, nbytes - direct_len, nt);
   if (close(fd) != 0 && !err) err = errno;
   if (err) return set_err(TSB_EIO, "%s(%s) failed: %s", write ? "write" : "read", path, strerror(err));
+  return TSB_OK;
+}
+
+int tsb_file_write_streamed(TsbCtx* ctx, const char* path, const void* hptr, uint64_t nbytes, const TsbEvent* events,
+                            const uint64_t* ends, uint32_t n) {
+  if (!ctx || !path || (nbytes && !hptr) || (n && (!events || !ends))) return set_err(TSB_EINVAL, "null argument");
+  DeviceGuard guard(ctx->device);
+  int fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+  if (fd < 0) return set_err(TSB_EIO, "open(%s) failed: %s", path, strerror(errno));
+  uint64_t done = 0;
+  int err = 0, rc = TSB_OK;
+  for (uint32_t i = 0; i < n && !err && rc == TSB_OK; ++i) {
+    if (ends[i] <= done) continue;
+    cudaEvent_t e = nullptr;
+    rc = event_lookup(ctx, events[i], &e);
+    if (rc != TSB_OK) break;
+    cudaError_t ce = cudaEventSynchronize(e);
+    if (ce != cudaSuccess) {
+      rc = set_err(TSB_ECUDA, "cudaEventSynchronize failed: %s", cudaGetErrorString(ce));
+      break;
+    }
+    uint64_t upto = std::min(ends[i], nbytes);
+    // everything whose copy has finished by now goes out in one write
+    while (i + 1 < n && ends[i + 1] <= nbytes) {
+      cudaEvent_t nx = nullptr;
+      if (event_lookup(ctx, events[i + 1], &nx) != TSB_OK || cudaEventQuery(nx) != cudaSuccess) {
+        (void)cudaGetLastError();
+        break;
+      }
+      upto = ends[++i];
+    }
+    err = rw_range(fd, true, (char*)const_cast<void*>(hptr) + done, done, upto - done);
+    done = upto;
+  }
+  if (rc == TSB_OK && !err && done < nbytes) err = EIO;  // the events did not cover the buffer
+  if (close(fd) != 0 && !err) err = errno;
+  if (rc != TSB_OK) return rc;
+  if (err) return set_err(TSB_EIO, "write(%s) failed: %s", path, strerror(err));
   return TSB_OK;
 }
 

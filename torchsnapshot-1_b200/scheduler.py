@@ -403,18 +403,20 @@ async def execute_write_reqs(
         del pbuf
         await write_out(path, view, lambda: alloc.notify(nbytes))
 
-    async def stream_file(eng: Engine, feed: List[Tuple[int, int]], pbuf: PinnedBuffer, path: str) -> None:
-        """One file of a streamed batch: the plugin's writer thread follows the D2H copies chunk by chunk."""
+    async def stream_file(eng: Engine, feed: Tuple[Any, Any], pbuf: PinnedBuffer, path: str) -> None:
+        """One file of a streamed batch: the plugin's writer thread follows the D2H copies chunk by chunk.
+        `feed` = (event handles, end offsets): event i done => bytes [0, ends[i]) are in pinned memory."""
         ctx = eng.ctx
         nbytes = pbuf.nbytes
         view = pbuf.view()
         del pbuf
+        events, ends = [int(e) for e in feed[0]], [int(x) for x in feed[1]]
 
         def wait_more(done: int) -> int:
             """Called on the plugin's writer thread: blocks (GIL released) until bytes beyond `done` are in pinned
             memory, returns how many are."""
             upto = done
-            for ev, end in feed:
+            for ev, end in zip(events, ends):
                 if end <= done:
                     continue
                 if upto == done:
@@ -423,6 +425,9 @@ async def execute_write_reqs(
                     break
                 upto = end
             return upto
+
+        # a plugin that writes through libtsb200 can follow the events natively, in one GIL-free call
+        wait_more.native = (ctx, feed[0], feed[1])  # type: ignore[attr-defined]
 
         try:
             t_ready = time.monotonic()
@@ -433,7 +438,7 @@ async def execute_write_reqs(
             if _TRACE_WRITES:
                 stats.write_trace.append((t_ready - stats.begin, t_start - stats.begin, time.monotonic() - stats.begin, nbytes))
         finally:
-            for ev, _end in feed:
+            for ev in events:
                 ctx.event_release(ev)
             try:
                 view.release()
@@ -479,19 +484,11 @@ async def execute_write_reqs(
                         pbuf = got
                     batch.append((path, off, nbytes, pbuf))
                     i += 1
-                feeds: List[List[Tuple[int, int]]] = [[] for _ in batch]
-                pos = [0] * len(batch)
-                left = sum(1 for b in batch if b[2] > 0)
-                while left:
-                    for b, (_path, off, nbytes, pbuf) in enumerate(batch):
-                        if pos[b] >= nbytes:
-                            continue
-                        c = min(_STREAM_CHUNK, nbytes - pos[b])
-                        ctx.memcpy_d2h(STREAM_D2H, pbuf.ptr + pos[b], base + off + pos[b], c)
-                        pos[b] += c
-                        feeds[b].append((ctx.event_record(STREAM_D2H), pos[b]))
-                        if pos[b] >= nbytes:
-                            left -= 1
+                # one native call issues the whole batch (hundreds of copies and event records from Python would
+                # fight the writer threads for the GIL on the event-loop thread)
+                feeds = ctx.memcpy_d2h_interleaved(
+                    STREAM_D2H, [b[3].ptr for b in batch], [base + b[1] for b in batch], [b[2] for b in batch], _STREAM_CHUNK
+                )
                 for b, (path, _off, _n, pbuf) in enumerate(batch):
                     spawn(stream_file(eng, feeds[b], pbuf, path))
                 del batch, pbuf

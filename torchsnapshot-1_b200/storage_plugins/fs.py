@@ -36,8 +36,10 @@ class FSStoragePlugin(StoragePlugin):
         # TSB200_FS_DIRECT=1: page-cache bypass (O_DIRECT) for the aligned body of every transfer -- for real
         # block devices; tmpfs has no use for it
         self._flags = _native.FILE_DIRECT if knobs.is_fs_direct_enabled() else 0
-        if self._flags:
-            self.write_streamed = None  # type: ignore[assignment]  (O_DIRECT transfers want whole, aligned buffers)
+        if self._flags or type(self).write is not FSStoragePlugin.write:
+            # O_DIRECT transfers want whole, aligned buffers; and a subclass that customises `write` sees every
+            # write there, as whole buffers
+            self.write_streamed = None  # type: ignore[assignment]
 
     def _prepare(self, rel: str) -> str:
         path = os.path.join(self.root, rel)
@@ -73,6 +75,11 @@ class FSStoragePlugin(StoragePlugin):
 
     def _write_streamed_sync(self, path: str, buf: Any, wait_more: Any) -> None:
         n = len(buf)
+        native = getattr(wait_more, "native", None)
+        if native is not None and n:
+            ctx, events, ends = native  # wait for the copies and write, all inside libtsb200
+            ctx.file_write_streamed(path, readonly_buffer_address(buf), n, events, ends)
+            return
         fd = os.open(path, os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o644)
         try:
             view = memoryview(buf)
