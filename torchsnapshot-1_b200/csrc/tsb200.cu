@@ -588,7 +588,18 @@ int tsb_ctx_create(int device, uint64_t host_arena_max, uint64_t dev_arena_max, 
   }
   if (host_arena_max == 0) host_arena_max = 4ull << 30;
   if (dev_arena_max == 0) dev_arena_max = 16ull << 30;
-  ctx->host_arena = new Arena(true, host_arena_max, 256ull << 20, 4096);
+  // Pinned segments are all of one size -- the largest object the writer produces by default (512 MiB chunks and
+  // shard pieces) -- so any empty segment serves any request: an arena at its bound then waits for a block to
+  // come back instead of returning odd-sized empty segments to the driver and pinning new ones (unregister +
+  // unmap + first touch + cudaHostRegister, tens of milliseconds each, and cudaHostRegister stalls every other
+  // CUDA call of the process meanwhile).  TSB200_PINNED_SEGMENT_BYTES overrides.
+  uint64_t host_seg = 512ull << 20;
+  if (const char* v = getenv("TSB200_PINNED_SEGMENT_BYTES")) {
+    const long long x = atoll(v);
+    if (x >= (1ll << 20)) host_seg = (uint64_t)x;
+  }
+  if (host_seg > host_arena_max) host_seg = host_arena_max;
+  ctx->host_arena = new Arena(true, host_arena_max, host_seg, 4096);
   ctx->dev_arena = new Arena(false, dev_arena_max, 256ull << 20, 512);
   ctx->scratch_host = new Arena(true, 1ull << 30, 4ull << 20, 4096);
   ctx->scratch_dev = new Arena(false, 4ull << 30, 16ull << 20, 512);
