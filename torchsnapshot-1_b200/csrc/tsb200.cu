@@ -758,8 +758,11 @@ int tsb_event_record(TsbCtx* ctx, int stream, TsbEvent* ev) {
       idx = ctx->free_events.back();
       ctx->free_events.pop_back();
     } else {
+      // blocking-sync events: a thread that waits for one sleeps instead of spinning.  Dozens of writer threads
+      // follow the device->host copies through these (tsb_file_write_streamed); spinning, they took the cores
+      // away from the thread that waits for the pack kernel (async_take blocked 65 ms instead of 13).
       cudaEvent_t ne;
-      cudaError_t ce = cudaEventCreate(&ne);
+      cudaError_t ce = cudaEventCreateWithFlags(&ne, cudaEventBlockingSync);
       if (ce != cudaSuccess) return set_err(TSB_ECUDA, "cudaEventCreate failed: %s", cudaGetErrorString(ce));
       ctx->events.push_back(ne);
       ctx->event_gen.push_back(1);
