@@ -758,11 +758,8 @@ int tsb_event_record(TsbCtx* ctx, int stream, TsbEvent* ev) {
       idx = ctx->free_events.back();
       ctx->free_events.pop_back();
     } else {
-      // blocking-sync events: a thread that waits for one sleeps instead of spinning.  Dozens of writer threads
-      // follow the device->host copies through these (tsb_file_write_streamed); spinning, they took the cores
-      // away from the thread that waits for the pack kernel (async_take blocked 65 ms instead of 13).
       cudaEvent_t ne;
-      cudaError_t ce = cudaEventCreateWithFlags(&ne, cudaEventBlockingSync);
+      cudaError_t ce = cudaEventCreate(&ne);
       if (ce != cudaSuccess) return set_err(TSB_ECUDA, "cudaEventCreate failed: %s", cudaGetErrorString(ce));
       ctx->events.push_back(ne);
       ctx->event_gen.push_back(1);
@@ -1390,9 +1387,17 @@ int tsb_file_write_streamed(TsbCtx* ctx, const char* path, const void* hptr, uin
     cudaEvent_t e = nullptr;
     rc = event_lookup(ctx, events[i], &e);
     if (rc != TSB_OK) break;
-    cudaError_t ce = cudaEventSynchronize(e);
+    // Poll, asleep in between: up to 32 writer threads follow the copies at once, and spinning in
+    // cudaEventSynchronize they took the cores away from the thread that waits for the pack kernel (async_take
+    // blocked 65 ms instead of 13 on a 16-core host); blocking-sync events woke up late by the length of the
+    // whole copy queue.  A chunk takes ~0.6 ms to arrive, so 100 us of extra latency costs nothing.
+    cudaError_t ce;
+    while ((ce = cudaEventQuery(e)) == cudaErrorNotReady) {
+      (void)cudaGetLastError();
+      usleep(100);
+    }
     if (ce != cudaSuccess) {
-      rc = set_err(TSB_ECUDA, "cudaEventSynchronize failed: %s", cudaGetErrorString(ce));
+      rc = set_err(TSB_ECUDA, "cudaEventQuery failed: %s", cudaGetErrorString(ce));
       break;
     }
     uint64_t upto = std::min(ends[i], nbytes);
