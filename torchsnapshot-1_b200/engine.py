@@ -59,7 +59,11 @@ class Engine:
         if not torch.cuda.is_available():
             raise _native.TsbError("The B200 path needs a CUDA device; there is no CPU fallback.")
         free_hbm, _total = torch.cuda.mem_get_info(device)
-        host_default = min(8 * _GiB, int(psutil.virtual_memory().available * 0.25))
+        # pinned arena bound: a quarter of the available host memory shared by the GPUs of the box, at most 16 GiB
+        # per rank -- room for a batch of the largest objects the writer produces (16 x 512 MiB) to be in flight
+        # together, which is what keeps every writer thread busy (scheduler.drain_wave)
+        gpus = max(torch.cuda.device_count(), 1)
+        host_default = min(16 * _GiB, int(psutil.virtual_memory().available * 0.25) // gpus)
         host_bound = knobs.get_pinned_bytes(host_default)
         dev_bound = knobs.get_device_staging_bytes(int(free_hbm * 0.5))
         self.device = device
