@@ -247,13 +247,17 @@ class _Allocator:
                     pass
             await self._wait(eng, "pinned host")
 
-    def pinned_now(self, eng: Engine, nbytes: int) -> Optional[PinnedBuffer]:
-        """A pinned block if one can be had right now (within the budget, out of the segments the arena already
-        holds), else None: never waits."""
+    async def pinned_now(self, eng: Engine, nbytes: int) -> Optional[PinnedBuffer]:
+        """A pinned block if one can be had without waiting for a release (within the budget; out of the segments
+        the arena holds, or out of a new one pinned from a worker thread while the arena is below its bound),
+        else None."""
         if self.budget is not None and self.pinned_inflight > 0 and self.pinned_inflight + nbytes > self.budget:
             return None
         try:
-            buf = eng.pinned(nbytes, False)
+            try:
+                buf = eng.pinned(nbytes, False)
+            except ArenaFull:
+                buf = await asyncio.get_running_loop().run_in_executor(None, eng.pinned, nbytes)
         except ArenaFull:
             return None
         self.outstanding += 1
@@ -478,7 +482,7 @@ async def execute_write_reqs(
                     if not batch:
                         pbuf = await alloc.pinned(eng, nbytes)
                     else:
-                        got = alloc.pinned_now(eng, nbytes)
+                        got = await alloc.pinned_now(eng, nbytes)
                         if got is None:
                             break
                         pbuf = got
