@@ -246,6 +246,7 @@ class GPUSlabStager(BufferStager):
         for i in np.flatnonzero(~contiguous):
             regs += pack_regions(tensors[int(i)], int(offsets[i]))
         self._strided = regions_to_array(regs) if regs else None
+        self._template: Any = None
 
     def is_device_stageable(self) -> bool:
         return True
@@ -255,15 +256,17 @@ class GPUSlabStager(BufferStager):
 
     def pack_region_array(self, dst_addr: int) -> Any:
         """The slab's pack regions as a REGION_DTYPE array (members back to back at dst_addr)."""
-        dense = self._dense
-        arr = np.zeros(int(dense.sum()), dtype=_native.REGION_DTYPE)
-        arr["src"] = self._ptrs[dense]
-        arr["dst"] = self._offsets[dense].astype(np.uint64) + np.uint64(dst_addr)
-        arr["run_bytes"] = self._nbytes[dense].astype(np.uint64)
-        if self._strided is not None:
-            tail = self._strided.copy()
-            tail["dst"] += np.uint64(dst_addr)
-            arr = np.concatenate([arr, tail])
+        if self._template is None:  # built once per plan: destinations relative to the slab's first byte
+            dense = self._dense
+            arr = np.zeros(int(dense.sum()), dtype=_native.REGION_DTYPE)
+            arr["src"] = self._ptrs[dense]
+            arr["dst"] = self._offsets[dense].astype(np.uint64)
+            arr["run_bytes"] = self._nbytes[dense].astype(np.uint64)
+            if self._strided is not None:
+                arr = np.concatenate([arr, self._strided])
+            self._template = arr
+        arr = self._template.copy()
+        arr["dst"] += np.uint64(dst_addr)
         return arr
 
     def pack_regions(self, dst_addr: int) -> List[RegionTuple]:
@@ -414,8 +417,7 @@ class TakePlanCache:
             contiguous,
             [tensors[int(i)].stride() for i in np.flatnonzero(~contiguous)],
             [t.dtype for t in tensors],
-            np.fromiter(map(T.get_device, tensors), dtype=np.int64, count=n),
-        )
+        )  # (no device column: under unified addressing an address names its device)
 
     @staticmethod
     def _same(a: Tuple[Any, ...], b: Tuple[Any, ...]) -> bool:
@@ -426,7 +428,6 @@ class TakePlanCache:
             and np.array_equal(a[2], b[2])
             and a[3] == b[3]
             and a[4] == b[4]
-            and np.array_equal(a[5], b[5])
         )
 
     def get(self, config: Any, paths: List[str], tensors: List[Any]) -> Optional[Tuple[Dict[str, Any], List[WriteReq]]]:
