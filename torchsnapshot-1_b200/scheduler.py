@@ -451,7 +451,10 @@ async def execute_write_reqs(
             del view
             alloc.notify(nbytes)
 
-    async def drain_wave(eng: Engine, base: int, files: List[Tuple[str, int, int]], ev_pack: int) -> None:
+    staged_gate = asyncio.Event()
+
+    async def drain_wave(eng: Engine, base: int, files: List[Tuple[str, int, int]], ev_pack: int,
+                         gate: Optional[asyncio.Event] = None) -> None:
         """D2H of every file of a packed wave, then release of the wave's staging block.
 
         With a plugin that can follow the copies (`write_streamed`, the FS plugin) the files of a batch cross the
@@ -463,6 +466,8 @@ async def execute_write_reqs(
         ctx = eng.ctx
         streamed = _STREAM_WRITES and getattr(storage, "write_streamed", None) is not None
         try:
+            if gate is not None:
+                await gate.wait()
             ctx.stream_wait_event(STREAM_D2H, ev_pack)
             i = 0
             while i < len(files):
@@ -600,9 +605,16 @@ async def execute_write_reqs(
                 stats.pack_launched = time.monotonic()
                 if stats.first_pack_launched is None:
                     stats.first_pack_launched = stats.pack_launched
-                spawn(drain_wave(eng, base, files, ev_pack))
-                # give the drain a chance to queue its D2H copies before the next wave is planned
-                await asyncio.sleep(0)
+                if i < len(reqs):
+                    spawn(drain_wave(eng, base, files, ev_pack))
+                    # give the drain a chance to queue its D2H copies before the next wave is planned
+                    await asyncio.sleep(0)
+                else:
+                    # The last wave of this device: its copies are queued once the caller has been told that
+                    # the snapshot is consistent (the loop runs these tasks as soon as it is driven again: right
+                    # away in take, on the background thread of async_take).  Queuing a few hundred chunk copies
+                    # is milliseconds of event-loop time that async_take's caller would otherwise wait for.
+                    spawn(drain_wave(eng, base, files, ev_pack, staged_gate))
 
         # ---- 2. host staging under the memory budget (reference scheduler.py:255-329) --------------
         budget = memory_budget_bytes
@@ -635,10 +647,12 @@ async def execute_write_reqs(
         for eng, ev in pack_waits:
             await _wait_event(loop, executor, eng, ev)
         stats.staging_done = time.monotonic()
+        staged_gate.set()
         logger.info(f"Rank {rank} completed staging in {stats.staging_done - stats.begin:.3f} s")
     except BaseException:
         # nothing is left dangling when planning or staging fails half way: queued copies and writes are
         # cancelled, the worker threads let go (reference: the exception leaves the event loop to the caller)
+        staged_gate.set()
         for t in tasks:
             t.cancel()
         await asyncio.gather(*tasks, return_exceptions=True)
