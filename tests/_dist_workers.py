@@ -237,3 +237,61 @@ def replicated_paths_differ(rank, world, tmp):
     out = StateDict(common=torch.zeros_like(common), **{f"only_{rank}": torch.zeros_like(mine)})
     snap.restore({"s": out})
     assert torch.equal(out["common"], common) and torch.equal(out[f"only_{rank}"], mine)
+
+
+def repeated_replicated_takes(rank, world, tmp):
+    """A job that checkpoints the same replicated tensors again and again repeats its previous plan (no
+    planning, same files from the same ranks) as long as every rank can and the split of the writes still
+    stands; new values in the same tensors are what gets saved; a replaced tensor on ONE rank makes every rank
+    plan afresh.  Every snapshot restores to what the state held when it was taken."""
+    import _cases
+    from torchsnapshot_b200 import knobs
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict, _RepeatTake
+
+    state = StateDict({f"p{i}": _cases.raw_tensor(300 + i, [64 + i, 9], torch.float32) for i in range(30)})
+    state["epoch"] = 0
+    own = StateDict(r=torch.full((7,), float(rank)))
+
+    def check(snap, want, epoch):
+        out = StateDict({k: (torch.zeros_like(v) if isinstance(v, torch.Tensor) else -1) for k, v in want.items()})
+        out_own = StateDict(r=torch.zeros(7))
+        snap.restore({"m": out, "own": out_own})
+        for k, v in want.items():
+            if isinstance(v, torch.Tensor):
+                assert torch.equal(out[k], v), k
+        assert out["epoch"] == epoch and torch.equal(out_own["r"], own["r"])
+
+    snaps, wants = [], []
+    with knobs.override_slab_size_threshold_bytes(6000):
+        for epoch in range(4):
+            state["epoch"] = epoch
+            for v in state.values():
+                if isinstance(v, torch.Tensor):
+                    v.add_(1.0)
+            before = _RepeatTake.repeats
+            snaps.append(Snapshot.take(os.path.join(tmp, f"s{epoch}"), {"m": state, "own": own}, replicated=["m/**"]))
+            wants.append({k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in state.items()})
+            # per-rank entries next to the replicated ones: planned once, repeated from the second take on
+            assert _RepeatTake.repeats - before == (1 if epoch else 0), epoch
+        for epoch, (snap, want) in enumerate(zip(snaps, wants)):
+            check(snap, want, epoch)
+        # a purely replicated state dict: another plan (first take), then repeats
+        took = []
+        for epoch in range(4):
+            state["epoch"] = 10 + epoch
+            for v in state.values():
+                if isinstance(v, torch.Tensor):
+                    v.mul_(1.5)
+            if epoch == 3 and rank == 1:
+                state["p5"] = state["p5"].clone()  # one rank moved one tensor: nobody repeats
+            before = _RepeatTake.repeats
+            snap = Snapshot.take(os.path.join(tmp, f"t{epoch}"), {"m": state}, replicated=["**"])
+            took.append(_RepeatTake.repeats - before)
+            want = {k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in state.items()}
+            out = StateDict({k: (torch.zeros_like(v) if isinstance(v, torch.Tensor) else -1) for k, v in want.items()})
+            snap.restore({"m": out})
+            for k, v in want.items():
+                assert (torch.equal(out[k], v) if isinstance(v, torch.Tensor) else out[k] == v), (epoch, k)
+            m = snap.get_manifest()
+            assert m["0/m/p3"].replicated and "1/m/p3" not in m and m["0/m/epoch"].get_value() == 10 + epoch
+        assert took == [0, 1, 1, 0], took

@@ -74,3 +74,8 @@ def test_world_size_change_round_trip_inside_one_job(tmp_path, world):
 @pytest.mark.timeout(300)
 def test_replicated_globs_over_state_dicts_that_differ_between_ranks(tmp_path):
     _launch("replicated_paths_differ", tmp_path)
+
+
+@pytest.mark.timeout(300)
+def test_repeated_takes_of_replicated_state_repeat_the_plan(tmp_path):
+    _launch("repeated_replicated_takes", tmp_path)

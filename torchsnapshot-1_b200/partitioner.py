@@ -176,8 +176,79 @@ def _digest(parts: Any) -> str:
     return hashlib.blake2b(repr(parts).encode("utf-8"), digest_size=12).hexdigest()
 
 
+class Negotiation:
+    """What the ranks told each other in the partitioner's exchange: per rank (non-replicated bytes, digest of
+    its write loads, measured throughput, the caller's `agree_on` string, whether it still holds the plan it made
+    for these loads last time)."""
+
+    def __init__(self, gathered: List[Any], rank: int) -> None:
+        self.gathered = gathered
+        self.rank = rank
+
+    @property
+    def same_loads(self) -> bool:
+        return all(g[1] == self.gathered[0][1] for g in self.gathered)
+
+    @property
+    def everybody_can_repeat(self) -> bool:
+        return self.same_loads and all(g[4] for g in self.gathered)
+
+    def key(self) -> Any:
+        return (self.gathered[0][1], tuple(g[0] for g in self.gathered), len(self.gathered))
+
+
+# The assignment of the previous take with the same loads: {"key", "out" (per rank: [(path, idx)]), "bytes" (per
+# rank)}.  Kept while it stays within 8 % of the best finish time under the throughputs the ranks report now, so
+# that a job checkpointing the same state again and again writes the same files from the same ranks -- and every
+# rank can reuse its whole plan (snapshot.py) instead of planning a slightly different share each time.
+_last_assignment: Optional[Dict[str, Any]] = None
+_STICKY_SLACK = 1.08
+
+
+def negotiate(pg: Any, non_replicated_size: int, loads_digest: str, agree_on: Optional[str],
+              can_repeat: bool = False) -> Negotiation:
+    """The partitioner's exchange on its own (one small all-gather); raises RanksDisagree on every rank alike
+    when the `agree_on` strings differ."""
+    world = pg.get_world_size()
+    gathered: List[Any] = [None] * world
+    held = _last_assignment is not None and _last_assignment["digest"] == loads_digest
+    pg.all_gather_object(gathered, (non_replicated_size, loads_digest, observed_speed(), agree_on, bool(can_repeat and held)))
+    if any(g[3] != gathered[0][3] for g in gathered):
+        raise RanksDisagree("the ranks do not agree on " + repr([g[3] for g in gathered]))
+    return Negotiation(gathered, pg.get_rank())
+
+
+def previous_assignment_stands(neg: Negotiation) -> bool:
+    """True when every rank still holds the previous plan for these loads and the previous assignment is still
+    good enough for the throughputs reported now (the same answer on every rank: gathered data only)."""
+    if not neg.everybody_can_repeat or _last_assignment is None or _last_assignment["key"] != neg.key():
+        return False
+    speeds = [g[2] for g in neg.gathered]
+    if not all(speeds):
+        return True
+    finish = [(g[0] + b) / s for g, b, s in zip(neg.gathered, _last_assignment["bytes"], speeds)]
+    ideal = sum(g[0] + b for g, b in zip(neg.gathered, _last_assignment["bytes"])) / sum(speeds)
+    return max(finish) <= _STICKY_SLACK * ideal
+
+
+def _remember_assignment(neg: Negotiation, out: List[List[Tuple[str, int]]], sizes: Dict[Tuple[str, int], int]) -> None:
+    global _last_assignment
+    _last_assignment = {"key": neg.key(), "digest": neg.gathered[0][1], "out": out,
+                        "bytes": [sum(sizes[u] for u in mine) for mine in out]}
+
+
+def probe_if_unseeded(any_device_stageable: bool) -> None:
+    """First take of replicated CUDA state in this process: measure the link instead of assuming equal ones (the
+    estimate is refined by every take from then on, record_take_speed)."""
+    if any_device_stageable and observed_speed() is None:
+        seed = probe_speed()
+        if seed:
+            _speed_estimates[""] = seed
+
+
 def partition_write_reqs(
-    entries: Dict[str, Entry], write_reqs: Dict[str, List[WriteReq]], pg: Any, agree_on: Optional[str] = None
+    entries: Dict[str, Entry], write_reqs: Dict[str, List[WriteReq]], pg: Any, agree_on: Optional[str] = None,
+    negotiated: Optional[Negotiation] = None,
 ) -> Tuple[Dict[str, Entry], Dict[str, List[WriteReq]]]:
     """Keep, on this rank, only its share of the replicated write requests (reference
     partitioner.py:169-233).  Entries must be consolidated afterwards
@@ -212,20 +283,14 @@ def partition_write_reqs(
         sub = getattr(entry, "type", None) == "ChunkedTensor"
         for idx, wr in enumerate(write_reqs.get(path, [])):
             loads.append((path, idx, _write_req_size(wr), sub))
-    if observed_speed() is None and any(
-        getattr(wr.buffer_stager, "is_device_stageable", lambda: False)()
-        for path in replicated for wr in write_reqs.get(path, [])[:1]
-    ):
-        # first take of replicated CUDA state in this process: measure instead of assuming equal links (the
-        # estimate is refined by every take from then on, record_take_speed)
-        seed = probe_speed()
-        if seed:
-            _speed_estimates[""] = seed
-    gathered: List[Any] = [None] * world
-    pg.all_gather_object(gathered, (non_replicated_size, _digest(loads), observed_speed(), agree_on))
-    if any(g[3] != gathered[0][3] for g in gathered):
-        raise RanksDisagree("the ranks do not agree on " + repr([g[3] for g in gathered]))
-    if all(g[1] == gathered[0][1] for g in gathered):
+    if negotiated is None:
+        probe_if_unseeded(observed_speed() is None and any(
+            getattr(wr.buffer_stager, "is_device_stageable", lambda: False)()
+            for path in replicated for wr in write_reqs.get(path, [])[:1]
+        ))
+        negotiated = negotiate(pg, non_replicated_size, _digest(loads), agree_on)
+    gathered = negotiated.gathered
+    if negotiated.same_loads:
         base_loads = loads
     else:
         # rank 0's view defines the units, like the reference; a chunked entry is only split when every
@@ -234,7 +299,10 @@ def partition_write_reqs(
         pg.all_gather_object(full, loads)
         base_loads = [(p, i, s, False) for p, i, s, _sub in full[0]]
     speeds = [g[2] for g in gathered]
-    mine = sorted(assign_write_loads(base_loads, [g[0] for g in gathered], speeds if all(speeds) else None)[rank])
+    out = assign_write_loads(base_loads, [g[0] for g in gathered], speeds if all(speeds) else None)
+    if negotiated.same_loads:
+        _remember_assignment(negotiated, out, {(p, i): sz for p, i, sz, _sub in base_loads})
+    mine = sorted(out[rank])
     new_entries: Dict[str, Entry] = {k: v for k, v in entries.items() if k not in replicated}
     new_wrs: Dict[str, List[WriteReq]] = {k: v for k, v in write_reqs.items() if k not in replicated}
     for path, idx in mine:
@@ -248,7 +316,14 @@ def partition_write_reqs(
         else:
             new_entries[path] = entry
         new_wrs.setdefault(path, []).append(write_reqs[path][idx])
+    global last_partition_inputs
+    last_partition_inputs = (non_replicated_size, negotiated.gathered[rank][1])
     return new_entries, new_wrs
+
+
+# (non-replicated bytes, digest of the loads) this rank sent in its last partition_write_reqs: what it sends again,
+# without rebuilding the loads, when it repeats a take (snapshot.py)
+last_partition_inputs: Optional[Tuple[int, str]] = None
 
 
 def consolidate_replicated_entries(rank_to_entries: List[Dict[str, Entry]], dedup: bool = True) -> List[Dict[str, Entry]]:

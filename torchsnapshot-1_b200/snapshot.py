@@ -73,6 +73,10 @@ VERSION = "0.1.0"  # the metadata schema version the reference writes (torchsnap
 # bench.py and scripts/, a handful of clock reads per take
 last_take_phases: Dict[str, float] = {}
 
+# (what every rank sent in the manifest exchange of the last take, the metadata built from it): a job that
+# checkpoints the same state again sends the same bytes, and the document is the same
+_last_gathered_manifests: Optional[Tuple[Any, Any]] = None
+
 
 
 def _validate_app_state(app_state: AppState) -> None:
@@ -151,6 +155,129 @@ def _memory_budget(local_world_size: int) -> int:
     import psutil
 
     return min(int(psutil.virtual_memory().available * 0.6) // max(local_world_size, 1), _MAX_PER_RANK_MEMORY_BUDGET_BYTES)
+
+
+class _RepeatTake:
+    """The plan a rank of a multi-rank job made for its share of a replicated state dict, kept for the next take of
+    the same tensors: entries (after partitioning and slab batching) and write requests.
+
+    Eligible state dicts hold only containers, inline primitives and plain tensors of buffer-protocol dtypes that
+    are not chunked (a DDP model plus tensor-valued optimizer state).  The next take may repeat the plan
+    when (1) this rank's tensors are where and what they were (same paths, addresses, shapes, strides, dtypes:
+    `TakePlanCache.fingerprint`), (2) every other rank says the same of its own, and (3) the previous split of the
+    writes is still within 8 % of the best one for the throughputs reported now (partitioner.py) -- (2) and (3)
+    are decided from the gathered exchange, identically on every rank.  Anything else plans afresh.
+    TSB200_PLAN_CACHE=0 turns it off."""
+
+    last: Optional["_RepeatTake"] = None
+    repeats = 0  # takes that repeated the previous plan (introspection for tests and bench.py)
+
+    def __init__(self, config: Any, paths: List[str], fingerprint: Any) -> None:
+        self.config, self.paths, self.fingerprint = config, paths, fingerprint
+        self.nonrep = 0
+        self.digest = ""
+        self.object_entries: Dict[str, Entry] = {}
+        self.write_reqs: List[WriteReq] = []
+        self.swaps: List[Tuple[Any, Any]] = []  # (stager, logical path | list of logical paths)
+        self.primitive_paths: List[str] = []
+        self._columns: Any = None
+
+    @staticmethod
+    def candidate(flattened: Dict[str, Any], rank: int, world: int, globs: Set[str], prepare_func: Optional[Any],
+                  max_chunk: int) -> Optional["_RepeatTake"]:
+        from .batcher import TakePlanCache
+        from .io_preparer import PrimitivePreparer
+        from .serialization import _BUFFER_PROTOCOL_SET
+
+        if prepare_func is not None or not TakePlanCache.enabled():
+            return None
+        plain, param = torch.Tensor, torch.nn.Parameter
+        paths: List[str] = []
+        tensors: List[Any] = []
+        primitives: List[str] = []
+        for path, obj in flattened.items():
+            kind = type(obj)
+            if kind is plain or kind is param:
+                if obj.dtype not in _BUFFER_PROTOCOL_SET or obj.is_quantized or obj.layout != torch.strided:
+                    return None
+                paths.append(path)
+                tensors.append(obj)
+            elif PrimitivePreparer.should_inline(obj):
+                primitives.append(path)
+            else:
+                return None
+        if not tensors:
+            return None
+        config = (rank, world, tuple(sorted(globs)), max_chunk, knobs.get_slab_size_threshold_bytes(),
+                  knobs.is_batching_disabled(), tuple(primitives))
+        rt = _RepeatTake(config, paths, TakePlanCache.fingerprint(tensors))
+        rt.primitive_paths = primitives
+        return rt
+
+    def columns_for(self, manifest: Dict[str, Any]) -> Any:
+        """Wire form of this plan's entries (manifest.tensor_columns_of), when `manifest` carries those objects."""
+        if not self.object_entries:
+            return None
+        first = next(iter(self.object_entries))
+        if manifest.get(first) is not self.object_entries[first]:
+            return None
+        if self._columns is None:
+            from .manifest import tensor_columns_of
+
+            self._columns = tensor_columns_of(self.object_entries)
+        return self._columns
+
+    def matches(self, other: "_RepeatTake") -> bool:
+        from .batcher import TakePlanCache
+
+        return (self.config == other.config and self.paths == other.paths
+                and TakePlanCache._same(self.fingerprint, other.fingerprint))
+
+    @staticmethod
+    def remember(rt: "_RepeatTake", flattened: Dict[str, Any], object_entries: Dict[str, Entry],
+                 write_reqs: List[WriteReq]) -> None:
+        from . import partitioner
+        from .batcher import GPUSlabStager
+
+        if partitioner.last_partition_inputs is None:
+            return
+        by_id = {id(flattened[p]): p for p in rt.paths}
+        swaps: List[Tuple[Any, Any]] = []
+        try:
+            for wr in write_reqs:
+                stager = wr.buffer_stager
+                if isinstance(stager, GPUSlabStager):
+                    swaps.append((stager, [by_id[id(t)] for t in stager.tensors]))
+                elif hasattr(stager, "byte_range_to_buffer_stager"):
+                    for member in stager.byte_range_to_buffer_stager.values():
+                        swaps.append((member, by_id[id(member.tensor)]))
+                else:
+                    swaps.append((stager, by_id[id(stager.tensor)]))
+        except (KeyError, AttributeError):
+            return  # a stager that does not hold one of the flattened tensors as it is (a chunk view, ...): no repeat
+        if any(getattr(e, "type", None) != "Tensor" for e in object_entries.values()):
+            return
+        rt.nonrep, rt.digest = partitioner.last_partition_inputs
+        rt.object_entries, rt.write_reqs, rt.swaps = object_entries, write_reqs, swaps
+        _RepeatTake.last = rt
+
+    def reuse(self, flattened: Dict[str, Any], is_async: bool, replicated_paths: Set[str]
+              ) -> Tuple[Dict[str, Entry], List[WriteReq], Dict[str, Entry]]:
+        """The previous plan over this take's tensor objects (the stagers keep the caller's current aliases alive,
+        not last take's), plus this take's inline primitives."""
+        for stager, where in self.swaps:
+            if isinstance(where, list):
+                stager.tensors = [flattened[p] for p in where]
+            else:
+                stager.tensor = flattened[where]
+                stager.is_async_snapshot = is_async
+        primitives: Dict[str, Entry] = {}
+        for p in self.primitive_paths:
+            entry = PrimitiveEntry.from_object(flattened[p])
+            entry.replicated = p in replicated_paths
+            primitives[p] = entry
+        _RepeatTake.repeats += 1
+        return self.object_entries, self.write_reqs, primitives
 
 
 class _Ready:
@@ -376,13 +503,34 @@ class Snapshot:
         # the ranks turn out to differ are the candidate lists themselves exchanged (the reference's way,
         # snapshot.py:796-822) and the plan redone for the paths every rank has.
         replicated_paths = set(candidates)
-        object_entries, write_reqs_by_path, primitive_entries = plan(replicated_paths)
-        mark("prepare_write")
+        agree_on = _paths_digest(candidates) if world > 1 else None
+        # A multi-rank job that checkpoints the same replicated tensors again (same paths, addresses, shapes) and
+        # whose previous split of the writes still stands repeats its previous plan: the exchange still happens
+        # (it carries this take's throughputs, and tells everybody whether everybody can repeat), the planning
+        # does not (`_RepeatTake`).
+        repeat = _RepeatTake.candidate(flattened, rank, world, globs, prepare_func, max_chunk) if world > 1 and candidates else None
+        negotiated = None
+        repeated = False
+        object_entries: Dict[str, Entry] = {}
+        write_reqs: List[WriteReq] = []
         try:
-            object_entries, write_reqs_by_path = partition_write_reqs(
-                object_entries, write_reqs_by_path, pg, agree_on=_paths_digest(candidates) if world > 1 else None
-            )
+            if repeat is not None and _RepeatTake.last is not None and _RepeatTake.last.matches(repeat):
+                from .partitioner import negotiate, previous_assignment_stands
+
+                negotiated = negotiate(pg, _RepeatTake.last.nonrep, _RepeatTake.last.digest, agree_on, can_repeat=True)
+                if previous_assignment_stands(negotiated):
+                    object_entries, write_reqs, primitive_entries = _RepeatTake.last.reuse(
+                        flattened, is_async, replicated_paths)
+                    repeated = True
+                    mark("partition_gather")
+            if not repeated:
+                object_entries, write_reqs_by_path, primitive_entries = plan(replicated_paths)
+                mark("prepare_write")
+                object_entries, write_reqs_by_path = partition_write_reqs(
+                    object_entries, write_reqs_by_path, pg, agree_on=agree_on, negotiated=negotiated
+                )
         except RanksDisagree:
+            repeat = None
             seen: List[Any] = [None] * world
             pg.all_gather_object(seen, candidates)
             counts: Dict[str, int] = defaultdict(int)
@@ -392,11 +540,14 @@ class Snapshot:
             replicated_paths = {p for p in seen[0] if counts[p] == world}
             object_entries, write_reqs_by_path, primitive_entries = plan(replicated_paths)
             object_entries, write_reqs_by_path = partition_write_reqs(object_entries, write_reqs_by_path, pg)
-        mark("partition_gather")
-        write_reqs = [wr for wrs in write_reqs_by_path.values() for wr in wrs]
-        if not knobs.is_batching_disabled():
-            _, write_reqs = batch_write_requests(entries=list(object_entries.values()), write_reqs=write_reqs)
-        write_reqs += bulk_write_reqs  # GPU slabs last, like the reference (batcher.py:319)
+        if not repeated:
+            mark("partition_gather")
+            write_reqs = [wr for wrs in write_reqs_by_path.values() for wr in wrs]
+            if not knobs.is_batching_disabled():
+                _, write_reqs = batch_write_requests(entries=list(object_entries.values()), write_reqs=write_reqs)
+            write_reqs += bulk_write_reqs  # GPU slabs last, like the reference (batcher.py:319)
+            if repeat is not None:
+                _RepeatTake.remember(repeat, flattened, object_entries, write_reqs)
         manifest.update(primitive_entries)
         manifest.update(object_entries)
         mark("batch")
@@ -412,11 +563,15 @@ class Snapshot:
         else:
             from .batcher import take_plan_cache
 
+            columns = take_plan_cache.columns_for(manifest)
+            if columns is None and repeat is not None and _RepeatTake.last is not None:
+                columns = _RepeatTake.last.columns_for(manifest)
             parts: List[Any] = [None] * world
-            pg.all_gather_object(
-                parts, (bool(replicated_paths), encode_manifest(manifest, take_plan_cache.columns_for(manifest)))
-            )
-            if any(flag for flag, _blob in parts):
+            pg.all_gather_object(parts, (bool(replicated_paths), encode_manifest(manifest, columns)))
+            global _last_gathered_manifests
+            if _last_gathered_manifests is not None and _last_gathered_manifests[0] == parts:
+                metadata = _last_gathered_manifests[1]  # every rank sent what it sent last time: same document
+            elif any(flag for flag, _blob in parts):
                 manifests = consolidate_replicated_entries([decode_manifest(blob) for _flag, blob in parts])
                 global_manifest: Manifest = {}
                 for r, m in enumerate(manifests):
@@ -426,6 +581,7 @@ class Snapshot:
                 metadata = SnapshotMetadata(version=VERSION, world_size=world, manifest=global_manifest)
             else:
                 metadata = LazySnapshotMetadata(VERSION, world, [blob for _flag, blob in parts])
+            _last_gathered_manifests = (parts, metadata)
         mark("manifest_gather")
 
         pending = sync_execute_write_reqs(
