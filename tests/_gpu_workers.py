@@ -156,6 +156,22 @@ def ddp_replicated(rank, world, tmp):
         del os.environ["TSB200_P2P_RESHARD"]
     m = snap.get_manifest()
     assert all(m[f"0/m/p{i}"].replicated for i in range(12)) and "1/m/p0" not in m
+    # the next checkpoints of the same tensors repeat the plan (new values, same files from the same ranks)
+    from torchsnapshot_b200.snapshot import _RepeatTake
+
+    for round_ in range(2):
+        for v in state.values():
+            v.add_(1.0)
+        before = _RepeatTake.repeats
+        snap2 = Snapshot.take(os.path.join(tmp, f"snap_again{round_}"), {"m": state}, replicated=["**"])
+        assert _RepeatTake.repeats == before + 1, (round_, _RepeatTake.repeats, before)
+        out3 = StateDict({k: torch.zeros_like(v) for k, v in state.items()})
+        snap2.restore({"m": out3})
+        for k in state:
+            assert torch.equal(out3[k], state[k]), k
+        m2 = snap2.get_manifest()
+        assert {k: (e.location, e.byte_range) for k, e in m.items() if hasattr(e, "byte_range")} == {
+            k: (e.location, e.byte_range) for k, e in m2.items() if hasattr(e, "byte_range")}
 
 
 def _flat_cuda(world, rank, n=200003):
