@@ -67,6 +67,16 @@ __device__ __forceinline__ uint4 realign(const uint4& a, const uint4& b, uint32_
   return o;
 }
 
+// 16-byte load that asks L2 for the 64-byte half line only (see ld_unit below): for the short runs of the strided
+// kernel, where a miss promoted to the whole 128-byte line doubles the DRAM reads.
+template <bool HINT>
+__device__ __forceinline__ uint4 ld_vec16(const uint4* p) {
+  if (!HINT) return __ldg(p);
+  uint4 v;
+  asm volatile("ld.global.L2::64B.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
 // ---------------------------------------------------------------------------------------------
 // tile-table expansion (device side)
 // ---------------------------------------------------------------------------------------------
@@ -256,8 +266,8 @@ __device__ __forceinline__ void copy_vec_shifted(uint4* __restrict__ d4, const u
     for (int u = 0; u < TSB_UNROLL; ++u) st_stream(d4 + j + (uint64_t)u * NL, realign<SW>(a[u], b[u], sb));
   }
   for (; j < nvec; j += NL) {
-    uint4 a = __ldg(a4 + j);
-    uint4 b = __ldg(a4 + j + 1);
+    uint4 a = ld_vec16<(NL <= 8)>(a4 + j);
+    uint4 b = ld_vec16<(NL <= 8)>(a4 + j + 1);
     st_stream(d4 + j, realign<SW>(a, b, sb));
   }
 }
