@@ -198,7 +198,8 @@ class Negotiation:
 
 
 # The assignment of the previous take with the same loads: {"key", "out" (per rank: [(path, idx)]), "bytes" (per
-# rank)}.  Kept while it stays within 8 % of the best finish time under the throughputs the ranks report now, so
+# rank), "speeds" (what the ranks reported then)}.  Kept while no rank's share of the box's throughput has moved by
+# more than 8 % since, so
 # that a job checkpointing the same state again and again writes the same files from the same ranks -- and every
 # rank can reuse its whole plan (snapshot.py) instead of planning a slightly different share each time.
 _last_assignment: Optional[Dict[str, Any]] = None
@@ -224,17 +225,20 @@ def previous_assignment_stands(neg: Negotiation) -> bool:
     if not neg.everybody_can_repeat or _last_assignment is None or _last_assignment["key"] != neg.key():
         return False
     speeds = [g[2] for g in neg.gathered]
-    if not all(speeds):
-        return True
-    finish = [(g[0] + b) / s for g, b, s in zip(neg.gathered, _last_assignment["bytes"], speeds)]
-    ideal = sum(g[0] + b for g, b in zip(neg.gathered, _last_assignment["bytes"])) / sum(speeds)
-    return max(finish) <= _STICKY_SLACK * ideal
+    then = _last_assignment["speeds"]
+    if not all(speeds) or not all(then):
+        return all(speeds) == all(then)
+    # the split was made for the relative throughputs of that time: it stands while no rank's share of the
+    # box's throughput has moved by more than 8 % (whatever the granularity of the loads)
+    mean_now, mean_then = sum(speeds) / len(speeds), sum(then) / len(then)
+    return all(abs((a / mean_now) / (b / mean_then) - 1.0) <= _STICKY_SLACK - 1.0 for a, b in zip(speeds, then))
 
 
 def _remember_assignment(neg: Negotiation, out: List[List[Tuple[str, int]]], sizes: Dict[Tuple[str, int], int]) -> None:
     global _last_assignment
     _last_assignment = {"key": neg.key(), "digest": neg.gathered[0][1], "out": out,
-                        "bytes": [sum(sizes[u] for u in mine) for mine in out]}
+                        "bytes": [sum(sizes[u] for u in mine) for mine in out],
+                        "speeds": [g[2] for g in neg.gathered]}
 
 
 def probe_if_unseeded(any_device_stageable: bool) -> None:
