@@ -161,7 +161,7 @@ def record_take_speed(nbytes: int, ms: float, kind: Optional[str] = None) -> Non
     kind = _speed_context if kind is None else kind
     gbps = nbytes / ms / 1e6
     prev = _speed_estimates.get(kind)
-    _speed_estimates[kind] = gbps if prev is None else 0.5 * prev + 0.5 * gbps
+    _speed_estimates[kind] = gbps if prev is None else 0.65 * prev + 0.35 * gbps
 
 
 class RanksDisagree(RuntimeError):
@@ -199,11 +199,11 @@ class Negotiation:
 
 # The assignment of the previous take with the same loads: {"key", "out" (per rank: [(path, idx)]), "bytes" (per
 # rank), "speeds" (what the ranks reported then)}.  Kept while no rank's share of the box's throughput has moved by
-# more than 8 % since, so
+# more than 12 % since, so
 # that a job checkpointing the same state again and again writes the same files from the same ranks -- and every
 # rank can reuse its whole plan (snapshot.py) instead of planning a slightly different share each time.
 _last_assignment: Optional[Dict[str, Any]] = None
-_STICKY_SLACK = 1.08
+_STICKY_SLACK = 1.12
 
 
 def negotiate(pg: Any, non_replicated_size: int, loads_digest: str, agree_on: Optional[str],
@@ -229,7 +229,7 @@ def previous_assignment_stands(neg: Negotiation) -> bool:
     if not all(speeds) or not all(then):
         return all(speeds) == all(then)
     # the split was made for the relative throughputs of that time: it stands while no rank's share of the
-    # box's throughput has moved by more than 8 % (whatever the granularity of the loads)
+    # box's throughput has moved by more than 12 % (whatever the granularity of the loads)
     mean_now, mean_then = sum(speeds) / len(speeds), sum(then) / len(then)
     return all(abs((a / mean_now) / (b / mean_then) - 1.0) <= _STICKY_SLACK - 1.0 for a, b in zip(speeds, then))
 
