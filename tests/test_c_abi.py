@@ -122,3 +122,47 @@ def test_host_gather_splits_work_by_bytes():
         _native.host_gather([0], [srcs[3].ctypes.data], [16])
     with pytest.raises(ValueError):
         _native.host_gather([1, 2], [1], [1])
+
+
+@pytest.mark.gpu
+def test_interleaved_copies_and_streamed_file_writes(engine, tmp_path):
+    """tsb_memcpy_d2h_interleaved + tsb_file_write_streamed through the C-ABI: three device buffers of awkward
+    sizes cross the link chunk by chunk, round-robin, one event per chunk; a writer per buffer follows its events;
+    the files hold exactly the device bytes.  Also tsb_host_alloc_nogrow: a block out of the existing segments or
+    TSB_EAGAIN, never new pinned memory."""
+    import numpy as np
+
+    ctx = engine.ctx
+    chunk = 1 << 20
+    sizes = [(5 << 20) + 12345, 1, 3 << 20, 0]
+    g = torch.Generator(device="cuda").manual_seed(11)
+    srcs = [torch.randint(0, 256, (max(n, 1),), dtype=torch.uint8, device="cuda", generator=g)[:n] for n in sizes]
+    torch.cuda.synchronize()
+    hptrs = [ctx.host_alloc(max(n, 1)) for n in sizes]
+    try:
+        feeds = ctx.memcpy_d2h_interleaved(_native.STREAM_D2H, hptrs, [max(t.data_ptr(), 1) for t in srcs], sizes, chunk)
+        assert [len(ev) for ev, _ends in feeds] == [6, 1, 3, 0]
+        assert [int(ends[-1]) for _ev, ends in feeds if len(ends)] == [sizes[0], 1, sizes[2]]
+        for i, ((events, ends), n) in enumerate(zip(feeds, sizes)):
+            path = str(tmp_path / f"f{i}")
+            ctx.file_write_streamed(path, hptrs[i], n, events, ends)
+            with open(path, "rb") as f:
+                assert f.read() == srcs[i].cpu().numpy().tobytes(), i
+            for ev in events:
+                ctx.event_release(int(ev))
+        # events that do not cover the buffer are an error, not a short file that looks complete
+        events, ends = ctx.memcpy_d2h_interleaved(_native.STREAM_D2H, hptrs[:1], [srcs[0].data_ptr()], [2 << 20], chunk)[0]
+        with pytest.raises(_native.TsbError):
+            ctx.file_write_streamed(str(tmp_path / "short"), hptrs[0], 3 << 20, events, ends)
+        for ev in events:
+            ctx.event_release(int(ev))
+    finally:
+        for h in hptrs:
+            ctx.host_free(h)
+    # no-grow allocation: what the segments hold is handed out, more than that is refused without pinning
+    _in_use, reserved, _bound = ctx.arena_stats(0)
+    h = ctx.host_alloc_nogrow(1 << 20)
+    ctx.host_free(h)
+    with pytest.raises(_native.ArenaFull):
+        ctx.host_alloc_nogrow(reserved + (1 << 30))
+    assert ctx.arena_stats(0)[1] == reserved

@@ -74,6 +74,14 @@ class Arena {
     if (reserved_ + need > bound_) release_empty_segments();
     if (reserved_ + need > bound_) return set_err(TSB_EAGAIN, "%s arena full", host_ ? "host" : "device");
     uint64_t seg = std::max(need, seg_default_);
+    if (!host_ && need > seg_default_) {
+      // a staging block for a whole wave: an eighth of headroom, so that the next take, whose share of the
+      // replicated writes may be a few percent larger, fits the same segment (a fresh cudaMalloc of gigabytes
+      // with peer mappings present was seen to hold async_take up for tens of milliseconds)
+      const uint64_t g = 64ull << 20;
+      seg = (need + need / 8 + g - 1) / g * g;
+    }
+    if (reserved_ + seg > bound_) seg = std::max(need, bound_ - reserved_);
     if (reserved_ + seg > bound_) seg = bound_ - reserved_;
     uint64_t base = 0;
     cudaError_t e = raw_alloc(seg, &base);
