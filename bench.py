@@ -812,7 +812,8 @@ def main():
                            "h2d_bytes_per_step": int(restore_h2d), "nvlink_bytes_per_rank": int(restore_peer)}
         line["async_take_blocked_ms"] = round(sum(res["blocked_ms"]) / K, 2)
         line["async_take_blocked_note"] = {
-            "first_call_ms": round(first_blocked, 1),
+            "first_call_ms": round(first_blocked, 1), "median_ms": round(_median(res["blocked_ms"]), 2),
+            "max_ms": round(max(res["blocked_ms"]), 1),
             "what": ("timed steps checkpoint the same tensors as the step before, as a training loop does, so the "
                      "previous plan is reused after an address/shape check; first_call_ms is the first async_take of "
                      "the process (plans afresh; arenas already grown by the step's take)")}
