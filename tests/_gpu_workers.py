@@ -235,3 +235,33 @@ def elastic_roundtrip_gpu(rank, world, tmp, sub=None):
         assert t.item() > 0, "some shard boundary falls inside a saved piece, so some bytes cross NVLink"
     finally:
         del os.environ["TSB200_P2P_MIN_AMPLIFICATION"]
+
+
+def ranks_on_different_hosts(rank, world, tmp):
+    """A job that spans hosts (here: the ranks CLAIM different hostnames) must not try CUDA IPC between them:
+    restore takes the reference's storage-only path on every rank, for replicated and for sharded state."""
+    import _cases
+    import torchsnapshot_b200.snapshot as snapmod
+    from torchsnapshot_b200 import reshard
+    from torchsnapshot_b200.snapshot import Snapshot, StateDict
+
+    shape = [512, 64]
+    full = _cases.raw_tensor(78, shape, torch.float32)
+    src = _sharded(0, world, shape, full)
+    rep = StateDict({f"p{i}": _cases.raw_tensor(400 + i, [129, 17], torch.float32).cuda() for i in range(6)})
+    snap = Snapshot.take(os.path.join(tmp, "snap"), {"emb": StateDict(t=src), "rep": rep}, replicated=["rep/**"])
+    real = snapmod.socket.gethostname
+    snapmod.socket.gethostname = lambda: f"node-{rank}"
+    try:
+        dst = _sharded(1, world, shape)
+        out = StateDict({k: torch.zeros_like(v) for k, v in rep.items()})
+        reshard.last_stats = None
+        snap.restore({"emb": StateDict(t=dst), "rep": out})
+        assert reshard.last_stats is None, "no peer-to-peer path between hosts"
+    finally:
+        snapmod.socket.gethostname = real
+    for shard in dst.local_shards():
+        want = _cases.box_slice(full, (shard.metadata.shard_offsets, shard.metadata.shard_sizes)).cuda()
+        assert torch.equal(shard.tensor, want)
+    for k in rep:
+        assert torch.equal(out[k], rep[k]), k

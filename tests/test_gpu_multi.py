@@ -63,3 +63,8 @@ def test_elastic_reshard_between_world_sizes(tmp_path, save_world, load_world):
 def test_world_size_change_round_trip_inside_one_job(tmp_path):
     """2 -> 1 -> 2 with a sub-group as the smaller world (bench.py's pre-flight runs the same at N = 2, 4, 8)."""
     _launch("elastic_roundtrip_gpu", tmp_path)
+
+
+@pytest.mark.timeout(400)
+def test_ranks_on_different_hosts_restore_through_storage(tmp_path):
+    _launch("ranks_on_different_hosts", tmp_path)
