@@ -615,6 +615,7 @@ def p2p_restore_units(
             if ipc_failure:
                 return
             n = 0
+            by_owner: Dict[int, List[RegionTuple]] = {}  # copy regions, grouped by the rank whose memory they read
             for key, unit in mine_by_key.items():
                 owner = owners.get(key)
                 if owner is None or unit.need == 0 or (key in scatter and owner != rank):
@@ -626,7 +627,7 @@ def p2p_restore_units(
                     handle, offset = all_exports[owner]["shared"][key]
                     src_base = state.opened[(owner, handle)] + offset
                     stats.peer_bytes += unit.need
-                regions.extend(unit.regions(src_base))
+                by_owner.setdefault(owner, []).extend(unit.regions(src_base))
                 n += 1
                 if n % 8 == 0:
                     await asyncio.sleep(0)  # let the read pipeline dispatch
@@ -637,9 +638,15 @@ def p2p_restore_units(
                 offsets, _total = packed_layout(asked)
                 for key in asked:
                     for i, r in enumerate(my_regions[key]):
-                        regions.append((base + offsets[(key, i)], r[1], r[2], tuple(r[3]),
-                                        packed_strides(r[2], r[3]), tuple(r[5])))
+                        by_owner.setdefault(owner, []).append((base + offsets[(key, i)], r[1], r[2], tuple(r[3]),
+                                                               packed_strides(r[2], r[3]), tuple(r[5])))
                     stats.peer_bytes += mine_by_key[key].need
+            # The launch walks its tiles in table order, so the order of the regions is the order in which this
+            # rank visits its peers.  Every rank starts with its own staging and goes round the ring from there:
+            # at any moment the ranks read from DIFFERENT owners instead of all draining owner 0, then owner 1, ...
+            # (one owner's HBM and NVLink egress shared by all readers at once).
+            for owner in sorted(by_owner, key=lambda o: (o - rank) % world):
+                regions.extend(by_owner[owner])
 
         async def read_all() -> None:
             loop = asyncio.get_running_loop()
