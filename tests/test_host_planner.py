@@ -466,6 +466,13 @@ def test_bulk_read_planner_gives_the_per_entry_reads():
         got = rr.buffer_consumer.unpack_region_array(base)
         assert sorted(map(bytes, got)) == sorted(map(bytes, want))
         assert rr.buffer_consumer.consumed_nbytes() == rr.byte_range[1] - rr.byte_range[0]
+    # the size bound of a merged read cuts the same way (a budgeted read_object)
+    for bound in (20000, 100000):
+        leaf = []
+        for e, t in items:
+            rrs, _fut = prepare_read(e, t)
+            leaf += rrs
+        assert sorted(map(key, plan_cuda_reads(items, bound))) == sorted(map(key, batch_read_requests(leaf, bound)))
 
 
 def test_take_plan_cache_hits_only_on_identical_tensors():

@@ -529,43 +529,47 @@ def plan_cuda_reads(items: List[Tuple[Any, Any]], max_merged_bytes: Optional[int
     TensorIOPreparer.prepare_read per entry followed by batch_read_requests gives -- the ranged reads of one
     file merged into one read of [min lo, max hi), split at holes above 1 MiB and at the size bound -- with one
     consumer per read instead of one per member."""
-    import numpy as np
-
     limit = _MAX_MERGED_READ_BYTES if max_merged_bytes is None else max(int(max_merged_bytes), 1)
     T = torch.Tensor
-    by_location: Dict[str, List[int]] = defaultdict(list)
-    for i, (entry, _t) in enumerate(items):
-        by_location[entry.location].append(i)
+    n = len(items)
+    if n == 0:
+        return []
+    # columns, then one sort by (file, offset): the members of a file are contiguous afterwards
+    ids: Dict[str, int] = {}
+    file_id = np.fromiter((ids.setdefault(e.location, len(ids)) for e, _t in items), dtype=np.int64, count=n)
+    lo = np.fromiter((e.byte_range[0] for e, _t in items), dtype=np.int64, count=n)
+    hi = np.fromiter((e.byte_range[1] for e, _t in items), dtype=np.int64, count=n)
+    tensors_all = [t for _e, t in items]
+    ptrs = np.fromiter(map(T.data_ptr, tensors_all), dtype=np.uint64, count=n)
+    contiguous = np.fromiter(map(T.is_contiguous, tensors_all), dtype=np.bool_, count=n)
+    order = np.lexsort((lo, file_id))
+    file_id, lo, hi, ptrs, contiguous = file_id[order], lo[order], hi[order], ptrs[order], contiguous[order]
+    order_list = order.tolist()
+    # a new read starts with a new file, or after a hole above the limit (members of a slab never overlap, so the
+    # end of the previous member is the end of everything before it)
+    starts = np.flatnonzero(np.concatenate(([True], (file_id[1:] != file_id[:-1]) | (lo[1:] - hi[:-1] > _MAX_READ_HOLE_BYTES))))
+    bounds = starts.tolist() + [n]
+    locations = list(ids)
     out: List[ReadReq] = []
-    for location, idxs in by_location.items():
-        idxs.sort(key=lambda i: items[i][0].byte_range[0])
-        los = [items[i][0].byte_range[0] for i in idxs]
-        his = [items[i][0].byte_range[1] for i in idxs]
-        groups: List[Tuple[int, int]] = []  # [a, b) into idxs
-        a, lo, hi = 0, los[0], his[0]
-        for k in range(1, len(idxs)):
-            if los[k] - hi > _MAX_READ_HOLE_BYTES or max(hi, his[k]) - lo > limit:
-                groups.append((a, k))
-                a, lo, hi = k, los[k], his[k]
-            else:
-                hi = max(hi, his[k])
-        groups.append((a, len(idxs)))
-        for a, b in groups:
-            members = idxs[a:b]
-            tensors = [items[i][1] for i in members]
-            lo = min(los[a:b])
-            hi = max(his[a:b])
-            n = len(members)
+    for a, b in zip(bounds[:-1], bounds[1:]):
+        # the size bound: cut where the merged range would pass it
+        cuts = [a]
+        if int(hi[b - 1] - lo[a]) > limit:
+            begin = int(lo[a])
+            for k in range(a + 1, b):
+                if int(hi[k]) - begin > limit:
+                    cuts.append(k)
+                    begin = int(lo[k])
+        cuts.append(b)
+        for c, d in zip(cuts[:-1], cuts[1:]):
+            first, last = int(lo[c]), int(hi[c:d].max())
+            tensors = [tensors_all[i] for i in order_list[c:d]]
             out.append(ReadReq(
-                path=location,
+                path=locations[int(file_id[c])],
                 buffer_consumer=GPUSlabConsumer(
-                    int(tensors[0].get_device()), tensors,
-                    np.fromiter(map(T.data_ptr, tensors), dtype=np.uint64, count=n),
-                    np.asarray(los[a:b], dtype=np.int64) - lo,
-                    np.asarray(his[a:b], dtype=np.int64) - np.asarray(los[a:b], dtype=np.int64),
-                    np.fromiter(map(T.is_contiguous, tensors), dtype=np.bool_, count=n),
-                    hi - lo),
-                byte_range=(lo, hi),
+                    int(tensors[0].get_device()), tensors, ptrs[c:d], lo[c:d] - first, hi[c:d] - lo[c:d],
+                    contiguous[c:d], last - first),
+                byte_range=(first, last),
             ))
     return out
 

@@ -19,13 +19,26 @@ from ..engine import buffer_address, readonly_buffer_address
 from ..io_types import ReadIO, StoragePlugin, WriteIO
 
 
+_executors: Dict[Tuple[int, int], ThreadPoolExecutor] = {}
+_executors_lock = threading.Lock()
+
+
+def _shared_executor(workers: int) -> ThreadPoolExecutor:
+    key = (os.getpid(), workers)  # threads do not survive a fork: a forked child gets a pool of its own
+    with _executors_lock:
+        ex = _executors.get(key)
+        if ex is None:
+            ex = _executors[key] = ThreadPoolExecutor(max_workers=workers, thread_name_prefix="tsb-fs")
+        return ex
+
+
 class FSStoragePlugin(StoragePlugin):
     def __init__(self, root: str, storage_options: Optional[Dict[str, Any]] = None) -> None:
         self.root = root
         self._dir_cache: Set[str] = set()
-        self._executor = ThreadPoolExecutor(
-            max_workers=int(os.environ.get("TSB200_IO_CONCURRENCY", "32")), thread_name_prefix="tsb-fs"
-        )
+        # one pool of I/O threads per process and size: every Snapshot call makes a plugin of its own, and
+        # starting (then joining) 32 threads per call is milliseconds on the critical path of a take / restore
+        self._executor = _shared_executor(int(os.environ.get("TSB200_IO_CONCURRENCY", "32")))
         # TSB200_IO_THREADS pins the pwrite/pread workers per file; by default they follow the load
         self._io_threads = knobs.get_io_threads()
         from ..scheduler import io_concurrency
@@ -136,4 +149,4 @@ class FSStoragePlugin(StoragePlugin):
         os.remove(os.path.join(self.root, path))
 
     async def close(self) -> None:
-        self._executor.shutdown(wait=True)
+        return None  # the I/O threads are shared by the plugins of the process; every operation has been awaited
