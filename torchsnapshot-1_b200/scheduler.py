@@ -495,9 +495,16 @@ async def execute_write_reqs(
                     i += 1
                 # one native call issues the whole batch (hundreds of copies and event records from Python would
                 # fight the writer threads for the GIL on the event-loop thread)
-                feeds = ctx.memcpy_d2h_interleaved(
-                    STREAM_D2H, [b[3].ptr for b in batch], [base + b[1] for b in batch], [b[2] for b in batch], _STREAM_CHUNK
-                )
+                try:
+                    feeds = ctx.memcpy_d2h_interleaved(
+                        STREAM_D2H, [b[3].ptr for b in batch], [base + b[1] for b in batch], [b[2] for b in batch],
+                        _STREAM_CHUNK,
+                    )
+                except BaseException:
+                    for _path, _off, nbytes, pbuf in batch:  # nothing was handed to a writer: give the blocks back
+                        pbuf.release()
+                        alloc.notify(nbytes)
+                    raise
                 for b, (path, _off, _n, pbuf) in enumerate(batch):
                     spawn(stream_file(eng, feeds[b], pbuf, path))
                 del batch, pbuf

@@ -280,6 +280,21 @@ class _RepeatTake:
         return self.object_entries, self.write_reqs, primitives
 
 
+def clear_plan_caches() -> None:
+    """Drop the plans kept for the next take (`batcher.TakePlanCache`, `_RepeatTake`, the last metadata exchange).
+    They refer to the tensors of the LAST take only, but that is still a reference: a caller that frees a model
+    and wants its memory back before the next checkpoint calls this (or sets TSB200_PLAN_CACHE=0)."""
+    global _last_gathered_manifests
+    from .batcher import take_plan_cache
+    from .manifest import register_stable_entries
+
+    take_plan_cache.key = take_plan_cache.value = None
+    take_plan_cache._columns = None
+    register_stable_entries([])
+    _RepeatTake.last = None
+    _last_gathered_manifests = None
+
+
 class _Ready:
     """A future that is already resolved: the object restored in place."""
 
