@@ -300,6 +300,28 @@ def test_repeated_takes_reuse_the_plan_and_follow_changes(tmp_path):
         check(s5, dict(state))
 
 
+def test_overlapping_async_takes(tmp_path):
+    """A second async_take that begins while the first is still copying and writing in its background thread: the
+    second repeats the first one's plan (same tensors), both drain, each snapshot holds what the state held when
+    its take returned."""
+    g = torch.Generator(device="cuda").manual_seed(21)
+    state = StateDict({f"t{i}": torch.randn(1 << 20, device="cuda", generator=g) for i in range(80)})
+    want1 = {k: v.clone() for k, v in state.items()}
+    p1 = Snapshot.async_take(str(tmp_path / "a"), {"st": state})
+    for v in state.values():
+        v.mul_(-2.0)
+    want2 = {k: v.clone() for k, v in state.items()}
+    p2 = Snapshot.async_take(str(tmp_path / "b"), {"st": state})
+    for v in state.values():
+        v.zero_()
+    s2, s1 = p2.wait(), p1.wait()
+    for snap, want in ((s1, want1), (s2, want2)):
+        out = StateDict({k: torch.zeros_like(v) for k, v in want.items()})
+        snap.restore({"st": out})
+        for k in want:
+            assert torch.equal(out[k], want[k]), k
+
+
 def test_async_take_is_consistent_under_mutation(tmp_path):
     g = torch.Generator(device="cuda").manual_seed(1)
     state = StateDict({f"t{i}": torch.randn(1 << 18, device="cuda", generator=g) for i in range(40)})

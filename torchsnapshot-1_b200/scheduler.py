@@ -138,6 +138,7 @@ class _Stats:
         self.bytes = 0
         self.staging_done: Optional[float] = None
         self.pack_launched: Optional[float] = None
+        self.finished = False  # PendingIOWork.complete() has run (successfully or not)
         self.first_pack_launched: Optional[float] = None
         self.speed_context = ""  # kind of sink, for the partitioner's throughput history
         self.d2h_done: Optional[float] = None
@@ -191,6 +192,7 @@ class _Stats:
 
 
 last_write_stats: Optional[_Stats] = None  # introspection hook for bench.py
+_unreleased_stats: List[_Stats] = []  # takes that were still draining when a later take began
 
 
 class _ReadStats:
@@ -313,6 +315,7 @@ class PendingIOWork:
             raise
         finally:
             self.executor.shutdown(wait=False)
+            self.stats.finished = True  # its event handles may be released by the next take
         self.stats.writes_done = time.monotonic()
         if knobs.trim_arenas_after_use():
             for eng in {e for e, _a, _b, _n in self.stats.pack_events}:
@@ -346,11 +349,23 @@ async def execute_write_reqs(
     global last_write_stats
     loop = asyncio.get_running_loop()
     executor = ThreadPoolExecutor(max_workers=_MAX_PER_RANK_CPU_CONCURRENCY, thread_name_prefix="tsb-stage")
-    if last_write_stats is not None:
+    # Event handles of earlier takes go back once those takes have drained: an async_take may still be copying in
+    # its background thread (it waits on its pack event there) when the next take begins.
+    for old in list(_unreleased_stats):
+        if old.finished:
+            _unreleased_stats.remove(old)
+            if old is not last_write_stats:
+                try:
+                    old.release()
+                except Exception:
+                    pass
+    if last_write_stats is not None and last_write_stats.finished:
         try:
             last_write_stats.release()
         except Exception:
             pass
+    elif last_write_stats is not None:
+        _unreleased_stats.append(last_write_stats)
     stats = _Stats()
     last_write_stats = stats
     try:
@@ -660,6 +675,7 @@ async def execute_write_reqs(
         # nothing is left dangling when planning or staging fails half way: queued copies and writes are
         # cancelled, the worker threads let go (reference: the exception leaves the event loop to the caller)
         staged_gate.set()
+        stats.finished = True
         for t in tasks:
             t.cancel()
         await asyncio.gather(*tasks, return_exceptions=True)
