@@ -166,3 +166,40 @@ def test_interleaved_copies_and_streamed_file_writes(engine, tmp_path):
     with pytest.raises(_native.ArenaFull):
         ctx.host_alloc_nogrow(reserved + (1 << 30))
     assert ctx.arena_stats(0)[1] == reserved
+
+
+def test_fs_plugin_write_streamed_follows_the_callback(tmp_path):
+    """The plugin's optional `write_streamed` with a plain Python `wait_more` (what a plugin that does not write
+    through libtsb200 implements against): the file is written in the order and amounts the callback releases,
+    and holds exactly the buffer."""
+    import asyncio
+
+    import numpy as np
+
+    from torchsnapshot_b200.storage_plugins.fs import FSStoragePlugin
+
+    data = np.random.RandomState(5).randint(0, 256, size=(3 << 20) + 17).astype(np.uint8)
+    released = []
+
+    def wait_more(done):
+        upto = min(done + (1 << 20) + 3, data.nbytes)  # odd-sized steps
+        released.append((done, upto))
+        return upto
+
+    plugin = FSStoragePlugin(str(tmp_path))
+    loop = asyncio.new_event_loop()
+    try:
+        loop.run_until_complete(plugin.write_streamed("a/b/file", memoryview(data), wait_more))
+        loop.run_until_complete(plugin.write_streamed("empty", memoryview(data[:0]), wait_more))
+        loop.run_until_complete(plugin.close())
+    finally:
+        loop.close()
+    assert (tmp_path / "a" / "b" / "file").read_bytes() == data.tobytes()
+    assert (tmp_path / "empty").read_bytes() == b""
+    assert released[0] == (0, (1 << 20) + 3) and released[-1][1] == data.nbytes and len(released) == 4
+
+    class Custom(FSStoragePlugin):
+        async def write(self, write_io):
+            await super().write(write_io)
+
+    assert Custom(str(tmp_path)).write_streamed is None  # a subclass that customises write sees whole buffers there
