@@ -522,6 +522,33 @@ __device__ __forceinline__ void transpose_tile(const TsbRegion* __restrict__ r, 
   constexpr int ROWS = TSB_TRANSPOSE_THREADS / TILE;  // tile rows one pass of the CTA covers
   constexpr int PASSES = TILE / ROWS;
   const uint32_t c = tid % TILE, r0 = tid / TILE;  // this thread's column, and its row in pass 0
+  if (sizeof(T) == 2 && wJ == TILE && wL == TILE &&
+      ((((uint64_t)(uintptr_t)sp) | ((uint64_t)(uintptr_t)dp) | (uint64_t)sL | (uint64_t)dJ) & 3u) == 0) {
+    // 2-byte elements, full tile, rows 4-byte aligned on both sides: move PAIRS.  A warp then reads and writes
+    // 128 contiguous bytes per row instead of 64, and issues half the instructions (2.9 -> see DESIGN section 3).
+    constexpr int PITCH = TILE + 2;  // in elements: rows start 4-byte aligned, (PITCH / 2) odd -> conflict-free stores
+    uint16_t(*t16)[PITCH] = reinterpret_cast<uint16_t(*)[PITCH]>(smem_raw);
+    constexpr int PAIRS = TILE / 2;                      // u32 per row
+    constexpr int RPP = TSB_TRANSPOSE_THREADS / PAIRS;   // rows per pass
+    constexpr int NP = TILE / RPP;
+    const uint32_t q = tid % PAIRS, row0 = tid / PAIRS;
+    uint32_t w[NP];
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+      w[p] = *reinterpret_cast<const uint32_t*>(sp + (uint64_t)q * 4 + (int64_t)(row0 + p * RPP) * sL);
+#pragma unroll
+    for (int p = 0; p < NP; ++p) *reinterpret_cast<uint32_t*>(&t16[row0 + p * RPP][2 * q]) = w[p];
+    __syncthreads();
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      const uint32_t j = row0 + p * RPP;
+      w[p] = (uint32_t)t16[2 * q][j] | ((uint32_t)t16[2 * q + 1][j] << 16);
+    }
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+      *reinterpret_cast<uint32_t*>(dp + (int64_t)(row0 + p * RPP) * dJ + (uint64_t)q * 4) = w[p];
+    return;
+  }
   if (wJ == TILE && wL == TILE) {
     // full tile: every load of the thread is in flight before its first shared-memory store
     T v[PASSES];
