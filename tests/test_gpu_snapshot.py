@@ -300,6 +300,69 @@ def test_repeated_takes_reuse_the_plan_and_follow_changes(tmp_path):
         check(s5, dict(state))
 
 
+def test_bulk_planned_state_with_edge_cases(tmp_path, monkeypatch):
+    """A state dict large enough for the bulk planners, with the shapes that trip byte arithmetic: empty tensors,
+    0-d scalars, odd byte counts, strided and transposed views, every element size, a tensor of exactly the slab
+    threshold and one just below it.  Payload bytes per object equal the oracle's serialisation, the plan equals
+    the per-leaf planner's (TSB200_PLAN_CACHE off and a state below the bulk minimum take that path), and the
+    round trip -- into strided destinations too -- is exact."""
+    from torchsnapshot_b200 import snapshot as snapmod
+
+    threshold = 1 << 16
+    g = torch.Generator(device="cuda").manual_seed(33)
+
+    def rnd(shape, dtype):
+        es = torch.empty((), dtype=dtype).element_size()
+        n = 1
+        for x in shape:
+            n *= x
+        raw = torch.randint(0, 256, (max(n * es, 1),), dtype=torch.uint8, device="cuda", generator=g)[: n * es]
+        return raw.view(dtype).reshape(shape)
+
+    state = {}
+    dtypes = [torch.uint8, torch.int16, torch.bfloat16, torch.float32, torch.int64, torch.float64, torch.bool]
+    for i in range(90):
+        dt = dtypes[i % len(dtypes)]
+        state[f"t{i}"] = (rnd([37 + 11 * i], torch.uint8) > 127) if dt is torch.bool else rnd([37 + 11 * i], dt)
+    state["empty"] = torch.empty(0, 5, device="cuda")
+    state["empty1d"] = torch.empty(0, dtype=torch.int64, device="cuda")
+    state["scalar"] = torch.tensor(3.25, device="cuda")
+    state["odd"] = rnd([3, 7, 5], torch.uint8)
+    state["strided"] = rnd([64, 40], torch.float32)[:, ::2]
+    state["transposed"] = rnd([48, 80], torch.int16).t()
+    state["at_threshold"] = rnd([threshold], torch.uint8)  # a request of its own (>= threshold)
+    state["below_threshold"] = rnd([threshold - 1], torch.uint8)
+    assert len(snapmod._bulk_plannable(state, set(), 1, None, 512 << 20)) == len(state)
+
+    def take(path, cached):
+        monkeypatch.setenv("TSB200_PLAN_CACHE", "1" if cached else "0")
+        with knobs.override_slab_size_threshold_bytes(threshold):
+            return Snapshot.take(path, {"st": StateDict(state)})
+
+    snap = take(str(tmp_path / "bulk"), True)
+    payloads, meta = _payloads(str(tmp_path / "bulk"))
+    for k, t in state.items():
+        assert payloads[f"0/st/{k}"] == sha(_bytes(t)), k
+    assert meta["manifest"]["0/st/at_threshold"]["location"] == "0/st/at_threshold"
+    assert meta["manifest"]["0/st/below_threshold"]["location"].startswith("batched/")
+    # the per-leaf planner on the same state: same manifest modulo slab names
+    import torchsnapshot_b200.snapshot as sm
+
+    monkeypatch.setattr(sm, "_bulk_plannable", lambda *a, **k: [])
+    take(str(tmp_path / "leaf"), False)
+    _p2, meta_leaf = _payloads(str(tmp_path / "leaf"))
+    assert _normalise(meta) == _normalise(meta_leaf)
+    monkeypatch.undo()
+    # round trip, with strided destinations where the sources were strided
+    out = {k: torch.zeros_like(v) for k, v in state.items()}
+    out["strided"] = torch.zeros(64, 40, device="cuda")[:, ::2]
+    out["transposed"] = torch.zeros(48, 80, dtype=torch.int16, device="cuda").t()
+    out_sd = StateDict(out)
+    snap.restore({"st": out_sd})
+    for k, t in state.items():
+        assert out_sd[k].shape == t.shape and _bytes(out_sd[k]) == _bytes(t), k
+
+
 def test_overlapping_async_takes(tmp_path):
     """A second async_take that begins while the first is still copying and writing in its background thread: the
     second repeats the first one's plan (same tensors), both drain, each snapshot holds what the state held when
