@@ -332,7 +332,7 @@ def test_bulk_planned_state_with_edge_cases(tmp_path, monkeypatch):
     state["transposed"] = rnd([48, 80], torch.int16).t()
     state["at_threshold"] = rnd([threshold], torch.uint8)  # a request of its own (>= threshold)
     state["below_threshold"] = rnd([threshold - 1], torch.uint8)
-    assert len(snapmod._bulk_plannable(state, set(), 1, None, 512 << 20)) == len(state)
+    assert len(snapmod._bulk_plannable(state, set(), 1, None, 512 << 20).paths) == len(state)
 
     def take(path, cached):
         monkeypatch.setenv("TSB200_PLAN_CACHE", "1" if cached else "0")
@@ -348,7 +348,7 @@ def test_bulk_planned_state_with_edge_cases(tmp_path, monkeypatch):
     # the per-leaf planner on the same state: same manifest modulo slab names
     import torchsnapshot_b200.snapshot as sm
 
-    monkeypatch.setattr(sm, "_bulk_plannable", lambda *a, **k: [])
+    monkeypatch.setattr(sm, "_bulk_plannable", lambda *a, **k: None)
     take(str(tmp_path / "leaf"), False)
     _p2, meta_leaf = _payloads(str(tmp_path / "leaf"))
     assert _normalise(meta) == _normalise(meta_leaf)

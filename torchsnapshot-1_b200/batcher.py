@@ -289,9 +289,10 @@ class GPUSlabStager(BufferStager):
 def plan_cuda_tensors(
     paths: List[str], tensors: List[Any], storage_paths: List[str], replicated: List[bool],
     slab_size_threshold_bytes: Optional[int] = None, is_async_snapshot: bool = False,
-    max_chunk_size_bytes: Optional[int] = None,
+    max_chunk_size_bytes: Optional[int] = None, table: Optional[Any] = None,
 ) -> Tuple[Dict[str, Any], List[WriteReq]]:
-    """Entries and write requests of plain CUDA tensors of buffer-protocol dtypes, planned in bulk.
+    """Entries and write requests of plain CUDA tensors of buffer-protocol dtypes, planned in bulk.  `table` is
+    tensor_table.scan(tensors) when the caller already has it.
 
     The result is what TensorIOPreparer.prepare_write per tensor followed by batch_write_requests gives --
     same TensorEntry fields, same slab membership and byte ranges (members back to back in the order given, a
@@ -302,10 +303,8 @@ def plan_cuda_tensors(
     import numpy as np
 
     from .io_preparer import TensorBufferStager, _DTYPE_STRINGS
-    from .serialization import dtype_to_element_size
 
     threshold = slab_size_threshold_bytes or knobs.get_slab_size_threshold_bytes()
-    T = torch.Tensor
     entry_cls = _tensor_entry_class()
     new, serializer = _new_object, _BUFFER_PROTOCOL_VALUE
 
@@ -321,14 +320,19 @@ def plan_cuda_tensors(
     write_reqs: List[WriteReq] = []
     if n == 0:
         return entries, write_reqs
-    dtypes = [t.dtype for t in tensors]
-    nbytes = np.fromiter(map(T.numel, tensors), dtype=np.int64, count=n) * np.fromiter(
-        (dtype_to_element_size(d) for d in dtypes), dtype=np.int64, count=n)
-    ptrs = np.fromiter(map(T.data_ptr, tensors), dtype=np.uint64, count=n)
-    contiguous = np.fromiter(map(T.is_contiguous, tensors), dtype=np.bool_, count=n)
-    devices = np.fromiter(map(T.get_device, tensors), dtype=np.int64, count=n)
-    shapes = list(map(list, map(T.size, tensors)))
-    dtype_strs = [_DTYPE_STRINGS[d] for d in dtypes]
+    from . import tensor_table as tt
+
+    if table is None:
+        table = tt.scan(tensors)
+    if not (table[:, tt.KIND] == tt.PLAIN).all():
+        raise AssertionError("plan_cuda_tensors takes plain dense tensors only")
+    nbytes = tt.nbytes_of(table)
+    ptrs = tt.ptrs_of(table)
+    contiguous = table[:, tt.CONTIGUOUS] != 0
+    devices = table[:, tt.DEVICE]
+    shapes = tt.shapes_of(table)
+    code_strs = {c: _DTYPE_STRINGS[tt.dtype_of(c)] for c in np.unique(table[:, tt.DTYPE]).tolist()}
+    dtype_strs = [code_strs[c] for c in table[:, tt.DTYPE].tolist()]
     small = nbytes < threshold
     # tensors of `threshold` bytes or more: a request each, in order (reference batcher.py:289-291); those above
     # the chunk size get no entry here -- the caller's per-leaf planner chunks them
@@ -368,8 +372,8 @@ class TakePlanCache:
     """The last bulk plan of a process, reused by the next take of the same tensors.
 
     A training loop checkpoints the same state dict over and over: same paths, same tensors at the same
-    addresses with the same shapes.  Validating that (addresses, sizes, strides of the non-contiguous members,
-    dtypes, devices -- read through C-level iterators) costs less than half of planning again, and a take of
+    addresses with the same shapes.  Validating that (addresses, devices, dtypes, sizes, strides: one table
+    from tensor_table.scan, compared with the previous one) costs a small part of planning again, and a take of
     13 k tensors is mostly planning.  On a hit the entries and slab stagers of the previous plan are used as they
     are: the manifest gets the same TensorEntry objects (they are never mutated after planning) and the slab
     files the same `batched/<uuid>` names, inside the new snapshot's own directory.  Any difference -- one
@@ -407,34 +411,25 @@ class TakePlanCache:
         return os.environ.get("TSB200_PLAN_CACHE", "1").lower() not in ("0", "false")
 
     @staticmethod
-    def fingerprint(tensors: List[Any]) -> Tuple[Any, ...]:
-        T = torch.Tensor
-        n = len(tensors)
-        contiguous = np.fromiter(map(T.is_contiguous, tensors), dtype=np.bool_, count=n)
-        return (
-            np.fromiter(map(T.data_ptr, tensors), dtype=np.uint64, count=n),
-            list(map(T.size, tensors)),
-            contiguous,
-            [tensors[int(i)].stride() for i in np.flatnonzero(~contiguous)],
-            [t.dtype for t in tensors],
-        )  # (no device column: under unified addressing an address names its device)
+    def fingerprint(tensors: List[Any], table: Optional[Any] = None) -> Any:
+        """What has to be unchanged for a plan to stand: address, device, dtype, sizes, strides of every tensor
+        (the rows of tensor_table.scan)."""
+        if table is None:
+            from . import tensor_table
+
+            table = tensor_table.scan(tensors)
+        return table
 
     @staticmethod
-    def _same(a: Tuple[Any, ...], b: Tuple[Any, ...]) -> bool:
-        return (
-            len(a[1]) == len(b[1])
-            and np.array_equal(a[0], b[0])
-            and a[1] == b[1]
-            and np.array_equal(a[2], b[2])
-            and a[3] == b[3]
-            and a[4] == b[4]
-        )
+    def _same(a: Any, b: Any) -> bool:
+        return a.shape == b.shape and bool(np.array_equal(a, b))
 
-    def get(self, config: Any, paths: List[str], tensors: List[Any]) -> Optional[Tuple[Dict[str, Any], List[WriteReq]]]:
+    def get(self, config: Any, paths: List[str], tensors: List[Any], table: Optional[Any] = None
+            ) -> Optional[Tuple[Dict[str, Any], List[WriteReq]]]:
         if self.key is None or not self.enabled():
             return None
         cfg, cached_paths, fp = self.key
-        if cfg != config or cached_paths != paths or not self._same(fp, self.fingerprint(tensors)):
+        if cfg != config or cached_paths != paths or not self._same(fp, self.fingerprint(tensors, table)):
             self.misses += 1
             return None
         self.hits += 1
@@ -449,7 +444,7 @@ class TakePlanCache:
         return entries, write_reqs
 
     def put(self, config: Any, paths: List[str], tensors: List[Any], entries: Dict[str, Any],
-            write_reqs: List[WriteReq]) -> None:
+            write_reqs: List[WriteReq], table: Optional[Any] = None) -> None:
         if not self.enabled():
             return
         index = {id(t): i for i, t in enumerate(tensors)}
@@ -458,7 +453,7 @@ class TakePlanCache:
             stager = wr.buffer_stager
             ts = stager.tensors if isinstance(stager, GPUSlabStager) else [stager.tensor]
             members.append([index[id(t)] for t in ts])
-        self.key = (config, list(paths), self.fingerprint(tensors))
+        self.key = (config, list(paths), self.fingerprint(tensors, table))
         self.value = (entries, write_reqs, members)
         from .manifest import register_stable_entries
 
@@ -670,7 +665,7 @@ def batch_write_requests(
         if slab.buffer_stagers:
             batched.append(WriteReq(path=slab.location, buffer_stager=slab.build()))
 
-    by_location = _tensor_entries_by_location(entries)
+    by_location = _tensor_entries_by_location(entries) if relocation else {}
     for location, (new_location, lo, hi) in relocation.items():
         entry = by_location.get(location)
         if entry is None:

@@ -32,6 +32,9 @@ def _flattenable_dict(d: Dict[Any, Any]) -> bool:
     return all_str or len({str(k) for k in d}) == len(d)
 
 
+_CONTAINER_TYPES = frozenset((list, dict, OrderedDict))
+
+
 def flatten(obj: Any, prefix: str) -> Tuple[Manifest, Dict[str, Any]]:
     manifest: Manifest = {}
     flattened: Dict[str, Any] = {}
@@ -39,12 +42,21 @@ def flatten(obj: Any, prefix: str) -> Tuple[Manifest, Dict[str, Any]]:
     # iterative pre-order walk; children are pushed in reverse so dict order is preserved
     while stack:
         node, path = stack.pop()
-        if type(node) is list:
+        kind = type(node)
+        if kind is list:
             manifest[path] = ListEntry()
             stack.extend((elem, f"{path}/{i}") for i, elem in reversed(list(enumerate(node))))
-        elif type(node) in (dict, OrderedDict) and _flattenable_dict(node):
+        elif (kind is dict or kind is OrderedDict) and _flattenable_dict(node):
             keys = list(node.keys())
-            manifest[path] = DictEntry(keys=keys) if type(node) is dict else OrderedDictEntry(keys=keys)
+            manifest[path] = DictEntry(keys=keys) if kind is dict else OrderedDictEntry(keys=keys)
+            if len(keys) > 8 and _CONTAINER_TYPES.isdisjoint(map(type, node.values())):
+                # a dict of leaves (a model's state dict, the bulk of a 20 k-tensor checkpoint): its leaves are
+                # next in pre-order whatever is still waiting on the stack, so they go in as they are
+                if all(type(k) is str for k in keys) and "%" not in (joined := "".join(keys)) and "/" not in joined:
+                    flattened.update(zip([f"{path}/{k}" for k in keys], node.values()))
+                else:
+                    flattened.update(zip([f"{path}/{_encode(str(k))}" for k in keys], node.values()))
+                continue
             stack.extend((node[k], f"{path}/{_encode(str(k))}") for k in reversed(keys))
         else:
             flattened[path] = node

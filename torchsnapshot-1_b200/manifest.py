@@ -349,13 +349,18 @@ class SnapshotMetadata:
 # pickle an order of magnitude faster, and a receiver only rebuilds entries when somebody asks for them
 # (`SnapshotMetadata.lazy`): rank 0 in the thread that writes the metadata file, the others not at all unless
 # the snapshot object is used to restore.
-def encode_manifest(manifest: Manifest, tensor_columns: Optional[Any] = None) -> bytes:
+def encode_manifest(manifest: Manifest, tensor_columns: Optional[Any] = None, rest: Optional[Manifest] = None) -> bytes:
     """`manifest` as bytes.  `tensor_columns` = (entries dict, pickled columns) from an earlier call with the SAME
     TensorEntry objects (see `tensor_columns_of`) skips re-encoding them; they then come last in the decoded
-    manifest."""
+    manifest.  `rest`, with `tensor_columns`, is the caller's statement that `manifest` is exactly `rest` plus
+    the entries of `tensor_columns`: only `rest` is walked then."""
     import pickle
 
     cached: Dict[str, Any] = tensor_columns[0] if tensor_columns is not None else {}
+    if rest is not None and tensor_columns is not None:
+        if len(rest) + len(cached) != len(manifest):
+            raise AssertionError("encode_manifest: `rest` and the cached entries do not add up to the manifest")
+        manifest = rest
     paths, locations, serializers, dtypes, shapes, replicated, ranges, others = [], [], [], [], [], [], [], []
     for path, e in manifest.items():
         if type(e) is TensorEntry:

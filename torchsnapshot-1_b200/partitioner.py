@@ -274,8 +274,10 @@ def partition_write_reqs(
         raise NotImplementedError("TORCH_SNAPSHOT_DISABLE_PARTITIONER is not implemented.")
     world = pg.get_world_size()
     rank = pg.get_rank()
+    if world == 1:
+        return entries, write_reqs
     replicated = {k: v for k, v in entries.items() if is_replicated(v)}
-    if world == 1 or (not replicated and agree_on is None):
+    if not replicated and agree_on is None:
         # (with `agree_on` the exchange below is also the caller's agreement check: every rank takes part,
         # whether or not it has replicated entries of its own)
         return entries, write_reqs

@@ -26,7 +26,9 @@ import threading
 import time
 from collections import defaultdict
 from concurrent.futures import ThreadPoolExecutor
-from typing import Any, Callable, Dict, List, Optional, Set, Tuple
+from typing import Any, Callable, Dict, List, NamedTuple, Optional, Set, Tuple
+
+import numpy as np
 
 import torch
 
@@ -103,37 +105,71 @@ def _infer_replicated(replicated: List[str], app_state: AppState) -> List[str]:
     return out
 
 
+class _Bulk(NamedTuple):
+    """The leaves batcher.plan_cuda_tensors plans: paths, tensors, and their rows of tensor_table.scan."""
+    paths: List[str]
+    tensors: List[Any]
+    table: Any
+
+
 def _bulk_plannable(
-    flattened: Dict[str, Any], replicated_paths: Set[str], world: int, prepare_func: Optional[Any], max_chunk: int
-) -> List[str]:
-    """Paths of the leaves batcher.plan_cuda_tensors plans (plain CUDA tensors of buffer-protocol dtypes that
-    are not chunked), or [] when the per-leaf planner has to do everything: bulk planning must cover EVERY
-    member of the GPU slabs, or the slabs would not be the ones the reference forms (batcher.py:291-316).  So
-    none of it when batching is off, a prepare function is set, chunks can be smaller than a slab, or some
-    would-be slab member cannot be planned here: a sharded tensor (its pieces join slabs), a tensor subclass,
-    replicated state of a multi-rank job (the partitioner assigns it request by request)."""
+    flattened: Dict[str, Any], replicated_paths: Set[str], world: int, prepare_func: Optional[Any], max_chunk: int,
+    table: Optional[Any] = None,
+) -> Optional[_Bulk]:
+    """The leaves batcher.plan_cuda_tensors plans (plain CUDA tensors of buffer-protocol dtypes that are not
+    chunked), or None when the per-leaf planner has to do everything: bulk planning must cover EVERY member of
+    the GPU slabs, or the slabs would not be the ones the reference forms (batcher.py:291-316).  So none of it
+    when batching is off, a prepare function is set, chunks can be smaller than a slab, or some would-be slab
+    member cannot be planned here: a sharded tensor (its pieces join slabs), a tensor subclass, a tensor the
+    table does not describe, replicated state of a multi-rank job (the partitioner assigns it request by
+    request).  `table` is tensor_table.scan(list(flattened.values())) when the caller already has it."""
     if prepare_func is not None or knobs.is_batching_disabled():
-        return []
+        return None
     threshold = knobs.get_slab_size_threshold_bytes()
     if max_chunk < threshold:
-        return []
-    from .serialization import _BUFFER_PROTOCOL_SET
+        return None
+    from . import tensor_table as tt
 
-    out: List[str] = []
-    plain, param = torch.Tensor, torch.nn.Parameter
-    check_replicated = world > 1 and bool(replicated_paths)
-    for path, obj in flattened.items():
-        kind = type(obj)
-        if kind is plain or kind is param:
-            # (tensors above the chunk size are handed back by plan_cuda_tensors: their chunks are at least a
-            # slab long here, so they never join a slab)
-            if obj.is_cuda and obj.dtype in _BUFFER_PROTOCOL_SET:
-                if check_replicated and path in replicated_paths:
-                    return []
-                out.append(path)
-        elif _is_sharded_tensor(obj) or isinstance(obj, torch.Tensor):
-            return []
-    return out if len(out) >= 64 else []  # a handful of tensors plans just as fast the ordinary way
+    values = list(flattened.values())
+    if table is None:
+        table = tt.scan(values)
+    kind = table[:, tt.KIND]
+    if (kind >= tt.UNDESCRIBED).any():
+        return None
+    for i in np.flatnonzero(kind == tt.NOT_A_TENSOR).tolist():
+        if _is_sharded_tensor(values[i]):
+            return None
+    # (tensors above the chunk size are handed back by plan_cuda_tensors: their chunks are at least a slab long
+    # here, so they never join a slab)
+    chosen = (kind == tt.PLAIN) & (table[:, tt.DEVICE] >= 0) & _buffer_protocol_mask()[table[:, tt.DTYPE]]
+    count = int(chosen.sum())
+    if count < 64:  # a handful of tensors plans just as fast the ordinary way
+        return None
+    paths = list(flattened.keys())
+    if count == len(values):
+        tensors = values
+    else:
+        idx = np.flatnonzero(chosen)
+        table = table[idx]
+        idx = idx.tolist()
+        paths, tensors = [paths[i] for i in idx], [values[i] for i in idx]
+    if world > 1 and replicated_paths and not replicated_paths.isdisjoint(paths):
+        return None
+    return _Bulk(paths, tensors, table)
+
+
+_buffer_protocol_codes: Any = None
+
+
+def _buffer_protocol_mask() -> Any:
+    """Look-up table over tensor_table dtype codes: True for the dtypes serialised through the buffer protocol."""
+    global _buffer_protocol_codes
+    if _buffer_protocol_codes is None:
+        from . import tensor_table as tt
+        from .serialization import _BUFFER_PROTOCOL_SET
+
+        _buffer_protocol_codes = tt.dtype_mask(_BUFFER_PROTOCOL_SET)
+    return _buffer_protocol_codes
 
 
 @contextlib.contextmanager
@@ -184,33 +220,37 @@ class _RepeatTake:
 
     @staticmethod
     def candidate(flattened: Dict[str, Any], rank: int, world: int, globs: Set[str], prepare_func: Optional[Any],
-                  max_chunk: int) -> Optional["_RepeatTake"]:
+                  max_chunk: int, table: Optional[Any] = None) -> Optional["_RepeatTake"]:
+        """`table` is tensor_table.scan(list(flattened.values())) when the caller already has it."""
+        from . import tensor_table as tt
         from .batcher import TakePlanCache
         from .io_preparer import PrimitivePreparer
-        from .serialization import _BUFFER_PROTOCOL_SET
 
         if prepare_func is not None or not TakePlanCache.enabled():
             return None
-        plain, param = torch.Tensor, torch.nn.Parameter
-        paths: List[str] = []
-        tensors: List[Any] = []
-        primitives: List[str] = []
-        for path, obj in flattened.items():
-            kind = type(obj)
-            if kind is plain or kind is param:
-                if obj.dtype not in _BUFFER_PROTOCOL_SET or obj.is_quantized or obj.layout != torch.strided:
-                    return None
-                paths.append(path)
-                tensors.append(obj)
-            elif PrimitivePreparer.should_inline(obj):
-                primitives.append(path)
-            else:
-                return None
-        if not tensors:
+        values = list(flattened.values())
+        if table is None:
+            table = tt.scan(values)
+        kind = table[:, tt.KIND]
+        plain = kind == tt.PLAIN
+        if (kind >= tt.UNDESCRIBED).any() or not plain.any():
             return None
+        if not _buffer_protocol_mask()[table[plain, tt.DTYPE]].all():
+            return None
+        all_paths = list(flattened.keys())
+        primitives: List[str] = []
+        for i in np.flatnonzero(~plain).tolist():
+            if not PrimitivePreparer.should_inline(values[i]):
+                return None
+            primitives.append(all_paths[i])
+        if primitives:
+            paths = [all_paths[i] for i in np.flatnonzero(plain).tolist()]
+            table = table[plain]
+        else:
+            paths = all_paths
         config = (rank, world, tuple(sorted(globs)), max_chunk, knobs.get_slab_size_threshold_bytes(),
                   knobs.is_batching_disabled(), tuple(primitives))
-        rt = _RepeatTake(config, paths, TakePlanCache.fingerprint(tensors))
+        rt = _RepeatTake(config, paths, table)
         rt.primitive_paths = primitives
         return rt
 
@@ -458,6 +498,11 @@ class Snapshot:
         else:
             candidates = []
         max_chunk = knobs.get_max_chunk_size_bytes()
+        # address, device, dtype, sizes and strides of every leaf, read once (what the bulk planner and both plan
+        # caches look at)
+        from . import tensor_table
+
+        leaf_table = tensor_table.scan(list(flattened.values()))
 
         bulk_write_reqs: List[WriteReq] = []
 
@@ -467,19 +512,17 @@ class Snapshot:
             primitives: Dict[str, Entry] = {}
             # plain CUDA tensors are planned in one vectorised pass when they are ALL of the GPU slabs' members
             bulk_write_reqs.clear()
-            bulk = _bulk_plannable(flattened, replicated_paths, world, prepare_func, max_chunk)
+            found = _bulk_plannable(flattened, replicated_paths, world, prepare_func, max_chunk, leaf_table)
             bulk_entries: Dict[str, Entry] = {}
-            if bulk:
-                from .batcher import plan_cuda_tensors
+            if found is not None:
+                from .batcher import plan_cuda_tensors, take_plan_cache
 
-                from .batcher import take_plan_cache
-
-                tensors = [flattened[p] for p in bulk]
+                bulk, tensors, table = found
                 flags = [p in replicated_paths for p in bulk] if replicated_paths else None
                 # (sync / async is not part of the key: it only matters to CPU tensors, which are not planned here)
                 config = (rank, world, max_chunk, knobs.get_slab_size_threshold_bytes(),
                           tuple(flags) if flags is not None else None)
-                hit = take_plan_cache.get(config, bulk, tensors)
+                hit = take_plan_cache.get(config, bulk, tensors, table)
                 if hit is not None:
                     bulk_entries, wrs = hit
                 else:
@@ -489,9 +532,12 @@ class Snapshot:
                     else:
                         flags = [False] * len(bulk)
                         storage_paths = [own + p for p in bulk]
-                    bulk_entries, wrs = plan_cuda_tensors(bulk, tensors, storage_paths, flags, None, is_async, max_chunk)
-                    take_plan_cache.put(config, bulk, tensors, bulk_entries, wrs)
+                    bulk_entries, wrs = plan_cuda_tensors(bulk, tensors, storage_paths, flags, None, is_async, max_chunk,
+                                                          table)
+                    take_plan_cache.put(config, bulk, tensors, bulk_entries, wrs, table)
                 bulk_write_reqs.extend(wrs)
+                if len(bulk_entries) == len(flattened):  # every leaf was planned above, in the order of `flattened`
+                    return dict(bulk_entries), wrs_by_path, primitives
             for logical_path, obj in flattened.items():
                 if logical_path in bulk_entries:
                     objects[logical_path] = bulk_entries[logical_path]
@@ -518,12 +564,15 @@ class Snapshot:
         # the ranks turn out to differ are the candidate lists themselves exchanged (the reference's way,
         # snapshot.py:796-822) and the plan redone for the paths every rank has.
         replicated_paths = set(candidates)
-        agree_on = _paths_digest(candidates) if world > 1 else None
+        # (`globs` is the same on every rank after the first exchange: without any, no rank has replicated
+        # state, and there is nothing to agree on or to split)
+        agree_on = _paths_digest(candidates) if world > 1 and globs else None
         # A multi-rank job that checkpoints the same replicated tensors again (same paths, addresses, shapes) and
         # whose previous split of the writes still stands repeats its previous plan: the exchange still happens
         # (it carries this take's throughputs, and tells everybody whether everybody can repeat), the planning
         # does not (`_RepeatTake`).
-        repeat = _RepeatTake.candidate(flattened, rank, world, globs, prepare_func, max_chunk) if world > 1 and candidates else None
+        repeat = (_RepeatTake.candidate(flattened, rank, world, globs, prepare_func, max_chunk, leaf_table)
+                  if world > 1 and candidates else None)
         negotiated = None
         repeated = False
         object_entries: Dict[str, Entry] = {}
@@ -541,9 +590,10 @@ class Snapshot:
             if not repeated:
                 object_entries, write_reqs_by_path, primitive_entries = plan(replicated_paths)
                 mark("prepare_write")
-                object_entries, write_reqs_by_path = partition_write_reqs(
-                    object_entries, write_reqs_by_path, pg, agree_on=agree_on, negotiated=negotiated
-                )
+                if world > 1 and globs:
+                    object_entries, write_reqs_by_path = partition_write_reqs(
+                        object_entries, write_reqs_by_path, pg, agree_on=agree_on, negotiated=negotiated
+                    )
         except RanksDisagree:
             repeat = None
             seen: List[Any] = [None] * world
@@ -564,6 +614,7 @@ class Snapshot:
             if repeat is not None:
                 _RepeatTake.remember(repeat, flattened, object_entries, write_reqs)
         manifest.update(primitive_entries)
+        rest_of_manifest = dict(manifest)  # containers and inline primitives: what is not an object entry
         manifest.update(object_entries)
         mark("batch")
 
@@ -581,8 +632,15 @@ class Snapshot:
             columns = take_plan_cache.columns_for(manifest)
             if columns is None and repeat is not None and _RepeatTake.last is not None:
                 columns = _RepeatTake.last.columns_for(manifest)
+            # when the object entries are exactly the cached plan's (same objects, nothing else), only the rest
+            # of the manifest is walked
+            rest = None
+            if columns is not None and len(columns[0]) == len(object_entries) and len(object_entries) > 0:
+                last = next(reversed(object_entries))
+                if columns[0].get(last) is object_entries[last] and len(rest_of_manifest) + len(object_entries) == len(manifest):
+                    rest = rest_of_manifest
             parts: List[Any] = [None] * world
-            pg.all_gather_object(parts, (bool(replicated_paths), encode_manifest(manifest, columns)))
+            pg.all_gather_object(parts, (bool(replicated_paths), encode_manifest(manifest, columns, rest)))
             global _last_gathered_manifests
             if _last_gathered_manifests is not None and _last_gathered_manifests[0] == parts:
                 metadata = _last_gathered_manifests[1]  # every rank sent what it sent last time: same document
