@@ -24,6 +24,9 @@ def blocked(profile=None):
     if profile: profile.disable()
     b = 1e3 * (time.monotonic() - t0)
     phases = {k: round(v, 1) for k, v in snapmod.last_take_phases.items()}
+    st = scheduler.last_write_stats
+    phases["stage:begin,pack_launched,staged,returned (ms since the call)"] = [
+        round(1e3 * (x - t0), 1) for x in (st.begin, st.pack_launched, st.staging_done, t0 + b / 1e3)]
     snap = p.wait()
     return b, phases, snap, d
 

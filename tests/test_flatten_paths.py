@@ -1,0 +1,52 @@
+"""flatten / inflate: path grammar, order and container entries (reference flatten.py:18-224), with the shapes the
+fast paths of this build's flatten see: wide dicts of leaves, keys that need escaping, mixed key types."""
+from collections import OrderedDict
+
+import torch
+
+import tsb200_loader
+
+tsb200_loader.load()
+from torchsnapshot_b200.flatten import flatten, inflate  # noqa: E402
+
+
+def test_wide_dict_of_leaves_keeps_order_and_objects():
+    d = {f"layer{i}.weight": torch.zeros(1) for i in range(200)}
+    manifest, flat = flatten(d, "model")
+    assert list(manifest) == ["model"] and manifest["model"].keys == list(d)
+    assert list(flat) == [f"model/{k}" for k in d]
+    assert all(flat[f"model/{k}"] is v for k, v in d.items())
+
+
+def test_escaping_in_wide_and_narrow_dicts():
+    wide = {f"a/{i}%": i for i in range(40)}
+    _m, flat = flatten({"w": wide, "n": {"x/y": 1}}, "p/q")
+    assert list(flat)[:2] == ["p%2Fq/w/a%2F0%25", "p%2Fq/w/a%2F1%25"]
+    assert "p%2Fq/n/x%2Fy" in flat
+    assert inflate(_m, flat, "p/q") == {"w": wide, "n": {"x/y": 1}}
+
+
+def test_preorder_with_containers_between_leaves():
+    obj = OrderedDict([("a", 1), ("b", [10, {"c": 2}]), ("d", {str(i): i for i in range(12)}), ("e", 3)])
+    manifest, flat = flatten(obj, "k")
+    assert list(flat) == ["k/a", "k/b/0", "k/b/1/c"] + [f"k/d/{i}" for i in range(12)] + ["k/e"]
+    assert list(manifest) == ["k", "k/b", "k/b/1", "k/d"]
+    assert type(manifest["k"]).__name__ == "OrderedDictEntry" and type(manifest["k/d"]).__name__ == "DictEntry"
+    assert inflate(manifest, flat, "k") == obj
+
+
+def test_int_keys_and_colliding_keys():
+    ints = {i: i * i for i in range(20)}
+    manifest, flat = flatten({"s": ints, "bad": {1: "a", "1": "b"}, "odd": {(1, 2): 3}}, "k")
+    assert list(flat)[:3] == ["k/s/0", "k/s/1", "k/s/2"]
+    assert flat["k/bad"] == {1: "a", "1": "b"} and flat["k/odd"] == {(1, 2): 3}  # opaque leaves
+    out = inflate(manifest, flat, "k")
+    assert out["s"] == ints and list(out["s"])[0] == 0  # ints stay ints
+
+
+def test_empty_containers_and_scalars():
+    manifest, flat = flatten({"e": {}, "l": [], "x": None}, "k")
+    assert list(manifest) == ["k", "k/e", "k/l"] and list(flat) == ["k/x"]
+    assert inflate(manifest, flat, "k") == {"e": {}, "l": [], "x": None}
+    manifest, flat = flatten(5, "k")
+    assert manifest == {} and flat == {"k": 5}

@@ -520,31 +520,47 @@ class GPUSlabConsumer(BufferConsumer):
 
 def plan_cuda_reads(items: List[Tuple[Any, Any]], max_merged_bytes: Optional[int] = None) -> List[ReadReq]:
     """Read requests for slab members restored in place into plain CUDA tensors, planned in bulk: `items` are
-    (TensorEntry with a byte range, destination tensor of the entry's dtype and shape).  Gives the reads
-    TensorIOPreparer.prepare_read per entry followed by batch_read_requests gives -- the ranged reads of one
-    file merged into one read of [min lo, max hi), split at holes above 1 MiB and at the size bound -- with one
-    consumer per read instead of one per member."""
-    limit = _MAX_MERGED_READ_BYTES if max_merged_bytes is None else max(int(max_merged_bytes), 1)
-    T = torch.Tensor
+    (TensorEntry with a byte range, destination tensor of the entry's dtype and shape).  See
+    plan_cuda_read_columns, which does the work."""
+    from . import tensor_table as tt
+
     n = len(items)
     if n == 0:
         return []
-    # columns, then one sort by (file, offset): the members of a file are contiguous afterwards
     ids: Dict[str, int] = {}
     file_id = np.fromiter((ids.setdefault(e.location, len(ids)) for e, _t in items), dtype=np.int64, count=n)
     lo = np.fromiter((e.byte_range[0] for e, _t in items), dtype=np.int64, count=n)
     hi = np.fromiter((e.byte_range[1] for e, _t in items), dtype=np.int64, count=n)
-    tensors_all = [t for _e, t in items]
-    ptrs = np.fromiter(map(T.data_ptr, tensors_all), dtype=np.uint64, count=n)
-    contiguous = np.fromiter(map(T.is_contiguous, tensors_all), dtype=np.bool_, count=n)
-    order = np.lexsort((lo, file_id))
-    file_id, lo, hi, ptrs, contiguous = file_id[order], lo[order], hi[order], ptrs[order], contiguous[order]
+    tensors = [t for _e, t in items]
+    return plan_cuda_read_columns(list(ids), file_id, lo, hi, tensors, tt.scan(tensors), max_merged_bytes)
+
+
+def plan_cuda_read_columns(locations: List[str], file_id: Any, lo: Any, hi: Any, tensors: List[Any], table: Any,
+                           max_merged_bytes: Optional[int] = None) -> List[ReadReq]:
+    """Read requests for slab members restored in place into plain CUDA tensors, from columns: member i is bytes
+    [lo[i], hi[i]) of file locations[file_id[i]] and goes to tensors[i], whose row of tensor_table.scan is
+    table[i] (a plain CUDA tensor of the saved dtype and shape: the caller has checked).  Gives the reads
+    TensorIOPreparer.prepare_read per entry followed by batch_read_requests gives -- the ranged reads of one
+    file merged into one read of [min lo, max hi), split at holes above 1 MiB and at the size bound -- with one
+    consumer per read instead of one per member; members bound for different devices never share a read."""
+    from . import tensor_table as tt
+
+    limit = _MAX_MERGED_READ_BYTES if max_merged_bytes is None else max(int(max_merged_bytes), 1)
+    n = len(tensors)
+    if n == 0:
+        return []
+    ptrs = tt.ptrs_of(table)
+    contiguous = table[:, tt.CONTIGUOUS] != 0
+    devices = table[:, tt.DEVICE]
+    # one sort by (device, file, offset): the members of a file are contiguous afterwards
+    order = np.lexsort((lo, file_id, devices))
+    file_id, lo, hi, ptrs, contiguous, devices = file_id[order], lo[order], hi[order], ptrs[order], contiguous[order], devices[order]
     order_list = order.tolist()
-    # a new read starts with a new file, or after a hole above the limit (members of a slab never overlap, so the
-    # end of the previous member is the end of everything before it)
-    starts = np.flatnonzero(np.concatenate(([True], (file_id[1:] != file_id[:-1]) | (lo[1:] - hi[:-1] > _MAX_READ_HOLE_BYTES))))
+    # a new read starts with a new file (or device), or after a hole above the limit (members of a slab never
+    # overlap, so the end of the previous member is the end of everything before it)
+    starts = np.flatnonzero(np.concatenate(([True], (file_id[1:] != file_id[:-1]) | (devices[1:] != devices[:-1])
+                                            | (lo[1:] - hi[:-1] > _MAX_READ_HOLE_BYTES))))
     bounds = starts.tolist() + [n]
-    locations = list(ids)
     out: List[ReadReq] = []
     for a, b in zip(bounds[:-1], bounds[1:]):
         # the size bound: cut where the merged range would pass it
@@ -558,12 +574,11 @@ def plan_cuda_reads(items: List[Tuple[Any, Any]], max_merged_bytes: Optional[int
         cuts.append(b)
         for c, d in zip(cuts[:-1], cuts[1:]):
             first, last = int(lo[c]), int(hi[c:d].max())
-            tensors = [tensors_all[i] for i in order_list[c:d]]
             out.append(ReadReq(
                 path=locations[int(file_id[c])],
                 buffer_consumer=GPUSlabConsumer(
-                    int(tensors[0].get_device()), tensors, ptrs[c:d], lo[c:d] - first, hi[c:d] - lo[c:d],
-                    contiguous[c:d], last - first),
+                    int(devices[c]), [tensors[i] for i in order_list[c:d]], ptrs[c:d], lo[c:d] - first,
+                    hi[c:d] - lo[c:d], contiguous[c:d], last - first),
                 byte_range=(first, last),
             ))
     return out

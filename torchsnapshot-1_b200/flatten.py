@@ -21,15 +21,17 @@ def _decode(s: str) -> str:
     return s.replace("%2F", "/").replace("%25", "%")
 
 
+_STR_ONLY = {str}
+
+
 def _flattenable_dict(d: Dict[Any, Any]) -> bool:
-    all_str = True
-    for k in d:
-        if type(k) is not str:
-            all_str = False
-            if not isinstance(k, (str, int)):
-                return False
-    # distinct str keys cannot collide; mixed int/str keys may ("1" vs 1)
-    return all_str or len({str(k) for k in d}) == len(d)
+    kinds = set(map(type, d))
+    if not kinds or kinds == _STR_ONLY:
+        return True  # distinct str keys cannot collide
+    if not all(issubclass(k, (str, int)) for k in kinds):
+        return False
+    # mixed int/str keys may collide ("1" vs 1)
+    return len({str(k) for k in d}) == len(d)
 
 
 _CONTAINER_TYPES = frozenset((list, dict, OrderedDict))
@@ -52,7 +54,7 @@ def flatten(obj: Any, prefix: str) -> Tuple[Manifest, Dict[str, Any]]:
             if len(keys) > 8 and _CONTAINER_TYPES.isdisjoint(map(type, node.values())):
                 # a dict of leaves (a model's state dict, the bulk of a 20 k-tensor checkpoint): its leaves are
                 # next in pre-order whatever is still waiting on the stack, so they go in as they are
-                if all(type(k) is str for k in keys) and "%" not in (joined := "".join(keys)) and "/" not in joined:
+                if set(map(type, keys)) == _STR_ONLY and "%" not in (joined := "".join(keys)) and "/" not in joined:
                     flattened.update(zip([f"{path}/{k}" for k in keys], node.values()))
                 else:
                     flattened.update(zip([f"{path}/{_encode(str(k))}" for k in keys], node.values()))
@@ -65,31 +67,49 @@ def flatten(obj: Any, prefix: str) -> Tuple[Manifest, Dict[str, Any]]:
 
 def inflate(manifest: Manifest, flattened: Dict[str, Any], prefix: str) -> Any:
     prefix = _encode(prefix)
-    manifest = {k: v for k, v in manifest.items() if k.split("/")[0] == prefix}
-    flattened = {k: v for k, v in flattened.items() if k.split("/")[0] == prefix}
+    below = prefix + "/"
+    manifest = {k: v for k, v in manifest.items() if k == prefix or k.startswith(below)}
+    flattened = {k: v for k, v in flattened.items() if k == prefix or k.startswith(below)}
     if prefix in flattened:
         return flattened[prefix]
     if prefix not in manifest:
         raise AssertionError(f"{prefix} is absent in both manifest and flattened.")
     containers: Dict[str, Any] = {}
+    lists = set()
     for path, entry in manifest.items():
         kind = entry.type
-        containers[path] = [] if kind == "list" else (OrderedDict() if kind == "OrderedDict" else {})
-    children: Dict[str, Dict[str, Any]] = {}
-    for path, val in list(containers.items()) + list(flattened.items()):
-        if path == prefix:
-            continue
-        parent, _, key = path.rpartition("/")
-        children.setdefault(parent, {})[key] = val
-    for path, vals in children.items():
-        container = containers[path]
-        entry = manifest[path]
-        if isinstance(container, list):
-            for i in sorted(int(k) for k in vals):
-                container.append(vals[str(i)])
+        if kind == "list":
+            containers[path] = []
+            lists.add(path)
         else:
-            for key in entry.keys:  # original key objects (ints stay ints), original order
-                enc = _encode(str(key))
-                if enc in vals:
-                    container[key] = vals[enc]
+            containers[path] = OrderedDict() if kind == "OrderedDict" else {}
+    # elements of lists: whatever is there, in index order (a list entry does not say how long the list was)
+    elements: Dict[str, Dict[int, Any]] = {}
+    if lists:
+        for source in (containers, flattened):
+            for path, val in source.items():
+                parent, _, key = path.rpartition("/")
+                if parent in lists:
+                    elements.setdefault(parent, {})[int(key)] = val
+    missing = object()
+    for path, entry in manifest.items():
+        container = containers[path]
+        if path in lists:
+            found = elements.get(path)
+            if found:
+                container.extend(found[i] for i in sorted(found))
+            continue
+        # original key objects (ints stay ints), original order; children are looked up by their paths
+        keys = entry.keys
+        if len(keys) > 8 and set(map(type, keys)) == _STR_ONLY and "%" not in (joined := "".join(keys)) and "/" not in joined:
+            child_paths = [f"{path}/{k}" for k in keys]
+        else:
+            child_paths = [f"{path}/{_encode(str(k))}" for k in keys]
+        for key, child in zip(keys, child_paths):
+            val = flattened.get(child, missing)
+            if val is missing:
+                val = containers.get(child, missing)
+                if val is missing:
+                    continue
+            container[key] = val
     return containers[prefix]

@@ -335,6 +335,68 @@ def clear_plan_caches() -> None:
     _last_gathered_manifests = None
 
 
+class _RestoreView:
+    """One rank's entries under one stateful's prefix, split for `Snapshot._load_stateful`: slab members that
+    batcher.plan_cuda_read_columns can plan, as columns (what a destination has to match: dtype code, rank,
+    sizes; where the bytes are: file, byte range), container entries, and the rest, which is planned entry by
+    entry.  Made once per Snapshot object, rank and prefix; the entries are the manifest's own objects."""
+
+    def __init__(self, manifest: Manifest, merged_sd: Dict[str, ShardedTensorEntry], prefix: str) -> None:
+        from . import tensor_table as tt
+        from .serialization import _STRING_TO_DTYPE, Serializer
+
+        buffer_protocol = Serializer.BUFFER_PROTOCOL.value
+        self.manifest, self.merged_sd = manifest, merged_sd
+        self.containers: Manifest = {}
+        self.rest: List[Tuple[str, Entry]] = []
+        self.paths: List[str] = []
+        self.entries: List[Entry] = []
+        self.has_sharded = False
+        self.locations: List[str] = []
+        file_of: Dict[str, int] = {}
+        codes: List[int] = []
+        shapes: List[List[int]] = []
+        ranges: List[Any] = []
+        files: List[int] = []
+        replicated: List[bool] = []
+        prefix_slash = prefix + "/"
+        for logical_path, entry in manifest.items():
+            if not logical_path.startswith(prefix_slash) and logical_path != prefix:
+                continue
+            if is_container_entry(entry):
+                self.containers[logical_path] = entry
+                continue
+            if type(entry) is TensorEntry and entry.byte_range is not None and entry.serializer == buffer_protocol:
+                code = tt.dtype_code(_STRING_TO_DTYPE.get(entry.dtype))
+                if code >= 0 and len(entry.shape) <= tt.MAX_DIMS:
+                    self.paths.append(logical_path)
+                    self.entries.append(entry)
+                    codes.append(code)
+                    shapes.append(entry.shape)
+                    ranges.append(entry.byte_range)
+                    files.append(file_of.setdefault(entry.location, len(file_of)))
+                    replicated.append(bool(entry.replicated))
+                    continue
+            if isinstance(entry, ShardedTensorEntry):
+                self.has_sharded = True
+            self.rest.append((logical_path, entry))
+        n = len(self.paths)
+        self.index = set(self.paths)
+        self.locations = list(file_of)
+        self.dtype_codes = np.array(codes, dtype=np.int64)
+        self.ndims = np.fromiter(map(len, shapes), dtype=np.int64, count=n)
+        self.shapes = np.zeros((n, tt.MAX_DIMS), dtype=np.int64)
+        for d in range(tt.MAX_DIMS):
+            has = np.flatnonzero(self.ndims > d)
+            if has.size == 0:
+                break
+            self.shapes[has, d] = [shapes[i][d] for i in has.tolist()]
+        span = np.array(ranges, dtype=np.int64).reshape(n, 2)
+        self.los, self.his = span[:, 0].copy(), span[:, 1].copy()
+        self.file_ids = np.array(files, dtype=np.int64)
+        self.replicated = np.array(replicated, dtype=np.bool_)
+
+
 class _Ready:
     """A future that is already resolved: the object restored in place."""
 
@@ -714,15 +776,25 @@ class Snapshot:
     ) -> None:
         if stateful is None:
             return
-        manifest, merged_sd = self._manifest_for_rank(rank)
+        from . import tensor_table as tt
+
+        prefix = _encode(key)
         # load straight into the tensors the stateful already owns (no second copy of the state)
         _, flattened = flatten(stateful.state_dict(), prefix=key)
-        flattened = {k: v for k, v in flattened.items() if isinstance(v, torch.Tensor) or _is_sharded_tensor(v)}
-        # sharded tensors follow what this state dict asks for: requested ones this rank did not save are
-        # added, saved ones nobody asks for are dropped
-        handle_sharded_tensor_elasticity(manifest, merged_sd, list(flattened.keys()))
-        prefix = _encode(key)
-        containers: Manifest = {}
+        # address, device, dtype, sizes and strides of every leaf, read once; only tensors and sharded tensors
+        # are destinations
+        paths, values = list(flattened.keys()), list(flattened.values())
+        table = tt.scan(values)
+        keep = table[:, tt.KIND] != tt.NOT_A_TENSOR
+        for i in np.flatnonzero(~keep).tolist():
+            if _is_sharded_tensor(values[i]):
+                keep[i] = True
+        if not keep.all():
+            idx = np.flatnonzero(keep)
+            table = table[idx]
+            idx = idx.tolist()
+            paths, values = [paths[i] for i in idx], [values[i] for i in idx]
+            flattened = dict(zip(paths, values))
         read_reqs: List[ReadReq] = []
         futs: Dict[str, Any] = {}
         # Sharded tensors and replicated state restored into CUDA tensors by every rank: each persisted
@@ -731,40 +803,11 @@ class Snapshot:
         device = torch.cuda.current_device() if (p2p_pg is not None and torch.cuda.is_available()) else -1
         sharded_p2p: List[Tuple[str, ShardedTensorEntry, Any]] = []
         shared_read_reqs: List[ReadReq] = []
-        # slab members restored in place into plain CUDA tensors are planned in one pass (batcher.plan_cuda_reads);
-        # with thousands of small tensors the per-entry planner is most of the time before the first read starts
-        bulk_items: List[Tuple[Any, Any]] = []
-        bulk_ok = not knobs.is_batching_disabled()
-        tensor_types = (torch.Tensor, torch.nn.Parameter)
-        from .serialization import _STRING_TO_DTYPE, Serializer
 
-        buffer_protocol = Serializer.BUFFER_PROTOCOL.value
-        prefix_slash = prefix + "/"
-        for logical_path, entry in manifest.items():
-            if not logical_path.startswith(prefix_slash) and logical_path != prefix:
-                continue
-            if is_container_entry(entry):
-                containers[logical_path] = entry
-                continue
-            obj_out = flattened.get(logical_path)
-            if (
-                bulk_ok
-                and type(entry) is TensorEntry
-                and entry.byte_range is not None
-                and entry.serializer == buffer_protocol
-                and type(obj_out) in tensor_types
-                and obj_out.is_cuda
-                and not (device >= 0 and entry.replicated)
-                and _STRING_TO_DTYPE.get(entry.dtype) == obj_out.dtype
-                and entry.shape == list(obj_out.shape)
-            ):
-                bulk_items.append((entry, obj_out))
-                futs[logical_path] = _Ready(obj_out)
-                flattened.pop(logical_path, None)
-                continue
+        def plan_entry(logical_path: str, entry: Entry, obj_out: Any) -> None:
             if isinstance(entry, ShardedTensorEntry):
                 if obj_out is None:
-                    continue  # sharded entries can only be loaded into a runtime object
+                    return  # sharded entries can only be loaded into a runtime object
                 if device >= 0:
                     from . import reshard
 
@@ -773,8 +816,7 @@ class Snapshot:
                         from .io_types import Future
 
                         futs[logical_path] = Future(obj=obj_out)
-                        flattened.pop(logical_path, None)
-                        continue
+                        return
             rrs, fut = prepare_read(entry=entry, obj_out=obj_out)
             if (
                 device >= 0
@@ -782,11 +824,71 @@ class Snapshot:
                 and rrs
                 and all(getattr(rr.buffer_consumer, "is_device_consumable", lambda: False)() for rr in rrs)
             ):
-                shared_read_reqs += rrs
+                shared_read_reqs.extend(rrs)
             else:
-                read_reqs += rrs
+                read_reqs.extend(rrs)
             futs[logical_path] = fut
-            flattened.pop(logical_path, None)
+
+        # Slab members restored in place into plain CUDA tensors of the saved dtype and shape are planned in one
+        # pass over columns (batcher.plan_cuda_reads): with thousands of small tensors the per-entry planner is
+        # most of the time before the first read starts.  The entries' side of those columns is made once per
+        # Snapshot object, rank and stateful (`_RestoreView`).
+        view = self._restore_view(rank, prefix)
+        bulk_reads: List[ReadReq] = []
+        if view.merged_sd or view.has_sharded:
+            # sharded tensors follow what this state dict asks for: requested ones this rank did not save are
+            # added, saved ones nobody asks for are dropped -- on a copy of the manifest, walked entry by entry
+            manifest = dict(view.manifest)
+            handle_sharded_tensor_elasticity(manifest, view.merged_sd, paths)
+            containers: Manifest = {}
+            prefix_slash = prefix + "/"
+            walk = []
+            for logical_path, entry in manifest.items():
+                if not logical_path.startswith(prefix_slash) and logical_path != prefix:
+                    continue
+                if is_container_entry(entry):
+                    containers[logical_path] = entry
+                elif logical_path not in view.index:
+                    walk.append((logical_path, entry))
+        else:
+            containers = view.containers
+            walk = view.rest
+        if view.paths and paths and not knobs.is_batching_disabled():
+            # rows of the destination table for the members, in the order of the view
+            if view.paths == paths:
+                rows = np.arange(len(paths), dtype=np.int64)
+            else:
+                position = {p: i for i, p in enumerate(paths)}
+                rows = np.fromiter((position.get(p, -1) for p in view.paths), dtype=np.int64, count=len(view.paths))
+            dest = table[np.maximum(rows, 0)]
+            eligible = (
+                (rows >= 0)
+                & (dest[:, tt.KIND] == tt.PLAIN)
+                & (dest[:, tt.DEVICE] >= 0)
+                & (dest[:, tt.DTYPE] == view.dtype_codes)
+                & (dest[:, tt.NDIM] == view.ndims)
+                & (dest[:, tt.SIZES:tt.SIZES + tt.MAX_DIMS] == view.shapes).all(axis=1)
+            )
+            if device >= 0:
+                eligible &= ~view.replicated  # replicated state of a multi-rank restore: read once, shared over NVLink
+            chosen = np.flatnonzero(eligible)
+            if chosen.size:
+                from .batcher import plan_cuda_read_columns
+
+                chosen_rows = rows[chosen]
+                tensors = [values[i] for i in chosen_rows.tolist()]
+                bulk_reads = plan_cuda_read_columns(
+                    view.locations, view.file_ids[chosen], view.los[chosen], view.his[chosen], tensors,
+                    table[chosen_rows])
+                futs.update(zip([view.paths[i] for i in chosen.tolist()], map(_Ready, tensors)))
+            left = np.flatnonzero(~eligible).tolist()
+        else:
+            left = range(len(view.paths))
+        for i in left:
+            logical_path = view.paths[i]
+            plan_entry(logical_path, view.entries[i], flattened.get(logical_path))
+        for logical_path, entry in walk:
+            plan_entry(logical_path, entry, flattened.get(logical_path))
         if p2p_pg is not None and device >= 0:
             from . import reshard
 
@@ -806,10 +908,7 @@ class Snapshot:
                     read_reqs += rrs
         if not knobs.is_batching_disabled():
             read_reqs = batch_read_requests(read_reqs=read_reqs)
-        if bulk_items:
-            from .batcher import plan_cuda_reads
-
-            read_reqs += plan_cuda_reads(bulk_items)
+        read_reqs += bulk_reads
         sync_execute_read_reqs(
             read_reqs=read_reqs, storage=storage, memory_budget_bytes=budget, rank=rank, event_loop=event_loop
         )
@@ -846,6 +945,17 @@ class Snapshot:
         storage.sync_close(event_loop=event_loop)
         event_loop.close()
         return fut.obj
+
+    def _restore_view(self, rank: int, prefix: str) -> _RestoreView:
+        cache = self.__dict__.setdefault("_restore_views", {})
+        view = cache.get((rank, prefix))
+        if view is None:
+            rank_cache = self.__dict__.setdefault("_rank_views", {})
+            if rank not in rank_cache:
+                rank_cache[rank] = get_manifest_for_rank(self.metadata, rank)
+            manifest, merged = rank_cache[rank]
+            view = cache[(rank, prefix)] = _RestoreView(manifest, merged, prefix)
+        return view
 
     def _manifest_for_rank(self, rank: int) -> Tuple[Manifest, Dict[str, ShardedTensorEntry]]:
         """Per-rank view of the manifest, computed once per Snapshot object and rank (a restore with several
