@@ -51,4 +51,18 @@ for i in range(3):
 for sort in ("tottime", "cumulative"):
     prof = cProfile.Profile(); prof.enable(); snap.restore({"c3": outs}); prof.disable()
     print(f"--- restore under cProfile ({sort})"); show(prof, sort)
+# what a job that starts up does: a Snapshot object made from the path (the metadata file is parsed), one restore
+for i in range(3):
+    torch.cuda.synchronize(); t0 = time.monotonic(); fresh = Snapshot(d); fresh.metadata; t1 = time.monotonic()
+    fresh.restore({"c3": outs}); torch.cuda.synchronize()
+    rs = scheduler.last_read_stats
+    print(json.dumps({"fresh_snapshot_restore_ms": round(1e3 * (time.monotonic() - t0), 1), "metadata_ms": round(1e3 * (t1 - t0), 1),
+                      "read_begin_ms": round(1e3 * (rs.begin - t0), 1)}), flush=True)
+prof = cProfile.Profile(); prof.enable(); fresh = Snapshot(d); fresh.restore({"c3": outs}); prof.disable()
+print("--- fresh Snapshot(path).restore under cProfile (tottime)"); show(prof, "tottime")
+# a take that cannot reuse the previous plan (the tensors moved): plan caches dropped first
 shutil.rmtree(d)
+for i in range(3):
+    snapmod.clear_plan_caches()
+    b, phases, snap, d = blocked(); shutil.rmtree(d)
+    print(json.dumps({"blocked_ms_planning_afresh": round(b, 1), "phases": phases}), flush=True)

@@ -336,7 +336,16 @@ class SnapshotMetadata:
             import yaml  # legacy snapshots written as real yaml
 
             doc = yaml.load(yaml_str, Loader=Loader if Loader is not None else yaml.SafeLoader)
-        manifest = {path: entry_from_obj(o) for path, o in doc["manifest"].items()}
+        manifest: Manifest = {}
+        new, cls_tensor, keys = object.__new__, TensorEntry, _TENSOR_KEYS
+        for path, o in doc["manifest"].items():
+            if len(o) == 7 and o.get("type") == "Tensor" and tuple(o) == keys:
+                # the document already is the entry's attribute dict (practically every entry of a big snapshot)
+                e = new(cls_tensor)
+                e.__dict__ = o
+                manifest[path] = e
+            else:
+                manifest[path] = entry_from_obj(o)
         return cls(version=doc["version"], world_size=doc["world_size"], manifest=manifest)
 
 

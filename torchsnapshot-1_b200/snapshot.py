@@ -360,41 +360,53 @@ class _RestoreView:
         files: List[int] = []
         replicated: List[bool] = []
         prefix_slash = prefix + "/"
+        code_of: Dict[str, int] = {}  # dtype string -> table code (-1: not a dtype the table names)
+        max_dims = tt.MAX_DIMS
+        paths, entries, rest, containers = self.paths, self.entries, self.rest, self.containers
         for logical_path, entry in manifest.items():
             if not logical_path.startswith(prefix_slash) and logical_path != prefix:
                 continue
-            if is_container_entry(entry):
-                self.containers[logical_path] = entry
-                continue
-            if type(entry) is TensorEntry and entry.byte_range is not None and entry.serializer == buffer_protocol:
-                code = tt.dtype_code(_STRING_TO_DTYPE.get(entry.dtype))
-                if code >= 0 and len(entry.shape) <= tt.MAX_DIMS:
-                    self.paths.append(logical_path)
-                    self.entries.append(entry)
-                    codes.append(code)
-                    shapes.append(entry.shape)
-                    ranges.append(entry.byte_range)
-                    files.append(file_of.setdefault(entry.location, len(file_of)))
-                    replicated.append(bool(entry.replicated))
-                    continue
-            if isinstance(entry, ShardedTensorEntry):
-                self.has_sharded = True
-            self.rest.append((logical_path, entry))
+            if type(entry) is TensorEntry:
+                span = entry.byte_range
+                if span is not None and entry.serializer == buffer_protocol:
+                    dtype = entry.dtype
+                    code = code_of.get(dtype)
+                    if code is None:
+                        code = code_of[dtype] = tt.dtype_code(_STRING_TO_DTYPE.get(dtype))
+                    shape = entry.shape
+                    if code >= 0 and len(shape) <= max_dims:
+                        paths.append(logical_path)
+                        entries.append(entry)
+                        codes.append(code)
+                        shapes.append(shape)
+                        ranges.append(span)
+                        location = entry.location
+                        file_id = file_of.get(location)
+                        if file_id is None:
+                            file_id = file_of[location] = len(file_of)
+                        files.append(file_id)
+                        replicated.append(entry.replicated)
+                        continue
+                rest.append((logical_path, entry))
+            elif is_container_entry(entry):
+                containers[logical_path] = entry
+            else:
+                if isinstance(entry, ShardedTensorEntry):
+                    self.has_sharded = True
+                rest.append((logical_path, entry))
         n = len(self.paths)
         self.index = set(self.paths)
         self.locations = list(file_of)
         self.dtype_codes = np.array(codes, dtype=np.int64)
         self.ndims = np.fromiter(map(len, shapes), dtype=np.int64, count=n)
         self.shapes = np.zeros((n, tt.MAX_DIMS), dtype=np.int64)
-        for d in range(tt.MAX_DIMS):
-            has = np.flatnonzero(self.ndims > d)
-            if has.size == 0:
-                break
-            self.shapes[has, d] = [shapes[i][d] for i in has.tolist()]
-        span = np.array(ranges, dtype=np.int64).reshape(n, 2)
+        flat = np.fromiter(itertools.chain.from_iterable(shapes), dtype=np.int64, count=int(self.ndims.sum()))
+        first = np.cumsum(self.ndims) - self.ndims
+        self.shapes[np.repeat(np.arange(n), self.ndims), np.arange(flat.size) - np.repeat(first, self.ndims)] = flat
+        span = np.fromiter(itertools.chain.from_iterable(ranges), dtype=np.int64, count=2 * n).reshape(n, 2)
         self.los, self.his = span[:, 0].copy(), span[:, 1].copy()
         self.file_ids = np.array(files, dtype=np.int64)
-        self.replicated = np.array(replicated, dtype=np.bool_)
+        self.replicated = np.array(replicated, dtype=np.bool_)  # (None counts as not replicated)
 
 
 class _Ready:
