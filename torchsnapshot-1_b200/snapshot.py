@@ -1042,11 +1042,17 @@ class PendingSnapshot:
         self.thread = threading.Thread(
             target=self._complete, args=(pending_io_work, metadata, storage, event_loop), daemon=True
         )
+        # The thread's first act is to wait for this event, which gives the GIL straight back: the caller of
+        # async_take gets its handle before the thread starts queuing a few hundred copies (otherwise the two
+        # fight over the GIL for a millisecond or more of the caller's blocked time).
+        self._go = threading.Event()
         self.thread.start()
+        self._go.set()
 
     def _complete(self, pending: PendingIOWork, metadata: SnapshotMetadata, storage: StoragePlugin,
                   event_loop: asyncio.AbstractEventLoop) -> None:
         err: Optional[str] = None
+        self._go.wait(1.0)
         try:
             pending.sync_complete(event_loop)
         except BaseException as e:  # noqa: B902
