@@ -363,6 +363,14 @@ def test_bulk_planned_state_with_edge_cases(tmp_path, monkeypatch):
         assert out_sd[k].shape == t.shape and _bytes(out_sd[k]) == _bytes(t), k
 
 
+def test_restore_into_mixed_destinations_matches_the_per_entry_planner(tmp_path):
+    """tests/_mixed_restore.py on CUDA tensors: slab members planned over columns where the destination matches,
+    entry by entry where it does not, the same values either way."""
+    import _mixed_restore
+
+    _mixed_restore.run("cuda", tmp_path)
+
+
 def test_overlapping_async_takes(tmp_path):
     """A second async_take that begins while the first is still copying and writing in its background thread: the
     second repeats the first one's plan (same tensors), both drain, each snapshot holds what the state held when

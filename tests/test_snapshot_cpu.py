@@ -335,3 +335,11 @@ def test_large_cpu_tensors_are_read_straight_into_their_memory(tmp_path, monkeyp
     calls.clear()
     got = snap.read_object("0/st/bf", obj_out=torch.zeros(70000).bfloat16(), memory_budget_bytes=30000)
     assert torch.equal(got, bf) and len(calls) >= 5 and max(n for _p, _r, n in calls) <= 30000
+
+
+def test_restore_into_mixed_destinations(tmp_path):
+    """Destinations that match, are strided, have another dtype, are absent or a Tensor subclass: the saved
+    values come back, with batching on and off (tests/_mixed_restore.py; the GPU suite runs it on CUDA tensors)."""
+    import _mixed_restore
+
+    _mixed_restore.run("cpu", tmp_path)
