@@ -210,6 +210,66 @@ def object_collectives(rank, world, tmp):
     assert [c.offsets for c in keep_all["m/w"].chunks] == [[0, 0], [2, 0]]
 
 
+def slot_gather(rank, world, tmp):
+    """PGWrapper.all_gather_object: small objects in one fixed-slot collective, anything longer -- on ANY rank --
+    through dist.all_gather_object on every rank, the same answers either way; a sub-group has slots of its own."""
+    import os
+    import pickle
+
+    import torch.distributed as dist
+
+    from torchsnapshot_b200 import pg_wrapper
+    from torchsnapshot_b200.pg_wrapper import PGWrapper
+
+    pg = PGWrapper()
+    calls = {"fallback": 0}
+    plain = dist.all_gather_object
+
+    def counting(*a, **k):
+        calls["fallback"] += 1
+        return plain(*a, **k)
+
+    dist.all_gather_object = counting
+    try:
+        def gather(obj, **kw):
+            out = [None] * world
+            pg.all_gather_object(out, obj, **kw)
+            return out
+
+        assert gather(("hello", rank, {"x": [rank] * 3})) == [("hello", r, {"x": [r] * 3}) for r in range(world)]
+        assert gather(None) == [None] * world and gather(b"") == [b""] * world
+        assert calls["fallback"] == 0
+        # the longest pickle that fits, and one byte more, on the last rank only
+        room = pg_wrapper._SLOT_BYTES - 8
+        overhead = len(pickle.dumps(b"", protocol=pickle.HIGHEST_PROTOCOL)) + 8  # generous: framing grows with length
+        fits = b"x" * (room - overhead)
+        assert len(pickle.dumps(fits, protocol=pickle.HIGHEST_PROTOCOL)) <= room
+        assert gather(fits if rank == world - 1 else rank) == list(range(world - 1)) + [fits]
+        assert calls["fallback"] == 0
+        big = b"y" * (room + 1)
+        assert gather(big if rank == world - 1 else rank) == list(range(world - 1)) + [big]
+        assert calls["fallback"] == 1  # every rank fell back, because one rank's object was long
+        assert gather({"rank": rank}, large=True) == [{"rank": r} for r in range(world)]
+        assert calls["fallback"] == 2
+        os.environ["TSB200_SLOT_GATHER"] = "0"
+        assert gather(rank) == list(range(world)) and calls["fallback"] == 3
+        del os.environ["TSB200_SLOT_GATHER"]
+        # many rounds: the buffers are reused
+        for i in range(50):
+            assert gather((i, rank)) == [(i, r) for r in range(world)]
+        assert calls["fallback"] == 3
+        if world >= 4:
+            sub = dist.new_group(ranks=[1, 3])
+            if rank in (1, 3):
+                spg = PGWrapper(sub)
+                out = [None, None]
+                spg.all_gather_object(out, f"sub{rank}")
+                assert out == ["sub1", "sub3"]
+            assert gather("after") == ["after"] * world
+    finally:
+        dist.all_gather_object = plain
+
+
 def elastic_roundtrip_cpu(rank, world, tmp):
     """Taken by `world` ranks, restored by world/2 (a sub-group of the same job), taken again by those, restored
     by all: flat parameters in two dtypes, a row-wise table, replicated state -- on CPU tensors over gloo."""

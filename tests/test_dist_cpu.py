@@ -51,6 +51,12 @@ def test_async_take_commit_across_ranks(tmp_path):
 
 
 @pytest.mark.timeout(300)
+@pytest.mark.parametrize("world", [2, 4])
+def test_small_objects_are_gathered_in_fixed_slots(tmp_path, world):
+    _launch("slot_gather", tmp_path, world=world)
+
+
+@pytest.mark.timeout(300)
 def test_object_collectives_of_the_host_mirror(tmp_path):
     _launch("object_collectives", tmp_path)
 

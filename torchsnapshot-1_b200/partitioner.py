@@ -302,7 +302,7 @@ def partition_write_reqs(
         # rank 0's view defines the units, like the reference; a chunked entry is only split when every
         # rank chunked it identically
         full: List[Any] = [None] * world
-        pg.all_gather_object(full, loads)
+        pg.all_gather_object(full, loads, large=True)
         base_loads = [(p, i, s, False) for p, i, s, _sub in full[0]]
     speeds = [g[2] for g in gathered]
     out = assign_write_loads(base_loads, [g[0] for g in gathered], speeds if all(speeds) else None)
@@ -368,5 +368,5 @@ def consolidate_replicated_entries_dist(entries: Dict[str, Entry], pg: Any, dedu
     """Collective form of `consolidate_replicated_entries` (reference partitioner.py:306-316): gather every
     rank's entries, consolidate, keep this rank's."""
     gathered: List[Any] = [None] * pg.get_world_size()
-    pg.all_gather_object(obj_list=gathered, obj=entries)
+    pg.all_gather_object(obj_list=gathered, obj=entries, large=True)
     return consolidate_replicated_entries(rank_to_entries=gathered, dedup=dedup)[pg.get_rank()]

@@ -5,8 +5,11 @@ process, and every collective degenerates to a local assignment.  Only metadata 
 (replicated-write assignment, manifest gather, IPC handles); tensor payload never does.
 """
 
-from typing import Any, List, Optional
+import os
+import pickle
+from typing import Any, Dict, List, Optional
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -17,6 +20,61 @@ def _resolve_group(pg: Optional[Any]) -> Optional[Any]:
     if dist.is_available() and dist.is_initialized():
         return dist.group.WORLD
     return None
+
+
+_SLOT_BYTES = 4096  # per rank; 8 bytes of it carry the pickle's length
+
+
+def _slots_enabled() -> bool:
+    return os.environ.get("TSB200_SLOT_GATHER", "1").lower() not in ("0", "false")
+
+
+class _SlotGather:
+    """Buffers of one process group for the fixed-slot all-gather: a send slot and `world` receive slots, on the
+    device for NCCL (with pinned host mirrors) and on the host for gloo."""
+
+    def __init__(self, pg: Any) -> None:
+        self.pg = pg  # (kept: the state is looked up by id(pg))
+        self.world = dist.get_world_size(group=pg)
+        self.nccl = dist.get_backend(group=pg) == "nccl"
+        pin = self.nccl and torch.cuda.is_available()
+        self.host_send = torch.zeros(_SLOT_BYTES, dtype=torch.uint8, pin_memory=pin)
+        self.host_recv = torch.zeros(self.world * _SLOT_BYTES, dtype=torch.uint8, pin_memory=pin)
+        self.device: Optional[int] = None
+        self.dev_send = self.dev_recv = None
+        if self.nccl:
+            self.device = torch.cuda.current_device()
+            dev = torch.device("cuda", self.device)
+            self.dev_send = torch.zeros(_SLOT_BYTES, dtype=torch.uint8, device=dev)
+            self.dev_recv = torch.zeros(self.world * _SLOT_BYTES, dtype=torch.uint8, device=dev)
+        self.send_np = self.host_send.numpy()
+        self.recv_np = self.host_recv.numpy().reshape(self.world, _SLOT_BYTES)
+
+
+_slot_states: Dict[int, _SlotGather] = {}
+
+
+def _slot_gather(pg: Any, obj: Any) -> Optional[List[Any]]:
+    """Every rank's `obj`, or None when some rank's pickle is longer than a slot (then every rank gets None)."""
+    state = _slot_states.get(id(pg))
+    if state is None or state.pg is not pg or (state.nccl and state.device != torch.cuda.current_device()):
+        state = _slot_states[id(pg)] = _SlotGather(pg)
+    data = pickle.dumps(obj, protocol=pickle.HIGHEST_PROTOCOL)
+    n = len(data)
+    state.send_np[:8] = np.frombuffer(np.int64(n).tobytes(), dtype=np.uint8)
+    if n <= _SLOT_BYTES - 8:
+        state.send_np[8:8 + n] = np.frombuffer(data, dtype=np.uint8)
+    if state.nccl:
+        state.dev_send.copy_(state.host_send, non_blocking=True)
+        dist.all_gather_into_tensor(state.dev_recv, state.dev_send, group=pg)
+        state.host_recv.copy_(state.dev_recv, non_blocking=True)
+        torch.cuda.current_stream(state.device).synchronize()
+    else:
+        dist.all_gather(list(state.host_recv.view(state.world, _SLOT_BYTES).unbind(0)), state.host_send, group=pg)
+    lengths = state.recv_np[:, :8].copy().view(np.int64).reshape(-1)
+    if (lengths > _SLOT_BYTES - 8).any() or (lengths < 0).any():
+        return None
+    return [pickle.loads(state.recv_np[r, 8:8 + int(lengths[r])].tobytes()) for r in range(state.world)]
 
 
 class PGWrapper:
@@ -45,11 +103,21 @@ class PGWrapper:
         else:
             dist.barrier(group=self.pg)
 
-    def all_gather_object(self, obj_list: List[Any], obj: Any) -> None:
+    def all_gather_object(self, obj_list: List[Any], obj: Any, large: bool = False) -> None:
+        """obj_list[r] <- rank r's `obj`.  Small objects (the usual case here: paths, digests, throughputs, IPC
+        handles) travel in ONE collective over fixed slots (`_SlotGather`); when any rank's pickle does not fit,
+        every rank sees that in the gathered lengths and all of them repeat the exchange with
+        dist.all_gather_object (a size exchange, a padded gather and the copies around them).  `large` says the
+        caller expects big objects (a manifest): the slots are not tried.  It must be the same on every rank."""
         if self.pg is None:
             obj_list[0] = obj
-        else:
-            dist.all_gather_object(obj_list, obj, group=self.pg)
+            return
+        if not large and _slots_enabled():
+            gathered = _slot_gather(self.pg, obj)
+            if gathered is not None:
+                obj_list[:] = gathered
+                return
+        dist.all_gather_object(obj_list, obj, group=self.pg)
 
     def broadcast_object_list(self, obj_list: List[Any], src: int = 0) -> None:
         if self.pg is not None:

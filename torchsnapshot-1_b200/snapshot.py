@@ -671,7 +671,7 @@ class Snapshot:
         except RanksDisagree:
             repeat = None
             seen: List[Any] = [None] * world
-            pg.all_gather_object(seen, candidates)
+            pg.all_gather_object(seen, candidates, large=True)
             counts: Dict[str, int] = defaultdict(int)
             for paths in seen:
                 for p in paths:
@@ -714,7 +714,7 @@ class Snapshot:
                 if columns[0].get(last) is object_entries[last] and len(rest_of_manifest) + len(object_entries) == len(manifest):
                     rest = rest_of_manifest
             parts: List[Any] = [None] * world
-            pg.all_gather_object(parts, (bool(replicated_paths), encode_manifest(manifest, columns, rest)))
+            pg.all_gather_object(parts, (bool(replicated_paths), encode_manifest(manifest, columns, rest)), large=True)
             global _last_gathered_manifests
             if _last_gathered_manifests is not None and _last_gathered_manifests[0] == parts:
                 metadata = _last_gathered_manifests[1]  # every rank sent what it sent last time: same document
