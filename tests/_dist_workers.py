@@ -355,3 +355,27 @@ def repeated_replicated_takes(rank, world, tmp):
             m = snap.get_manifest()
             assert m["0/m/p3"].replicated and "1/m/p3" not in m and m["0/m/epoch"].get_value() == 10 + epoch
         assert took == [0, 1, 1, 0], took
+        # When no rank's manifest changed, only digests travel and the previous metadata document stands; a rank
+        # that has dropped its caches (or a changed value anywhere) makes every rank exchange manifests again.
+        from torchsnapshot_b200 import snapshot as snapmod
+
+        def take(name):
+            snap = Snapshot.take(os.path.join(tmp, name), {"m": state}, replicated=["**"])
+            out = StateDict({k: (torch.zeros_like(v) if isinstance(v, torch.Tensor) else -1) for k, v in state.items()})
+            snap.restore({"m": out})
+            for k, v in state.items():
+                assert (torch.equal(out[k], v) if isinstance(v, torch.Tensor) else out[k] == v), (name, k)
+            return snap
+
+        a, b = take("same_a"), take("same_b")
+        assert b.metadata is a.metadata
+        if rank == 1:
+            snapmod.clear_plan_caches()
+        c = take("same_c")
+        assert c.metadata is not b.metadata and c.get_manifest().keys() == b.get_manifest().keys()
+        d = take("same_d")  # (the rank that dropped its caches planned afresh: new slab names, new document)
+        e = take("same_e")
+        assert e.metadata is d.metadata
+        state["epoch"] = 99
+        f = take("same_f")
+        assert f.metadata is not e.metadata and f.get_manifest()["0/m/epoch"].get_value() == 99

@@ -358,8 +358,10 @@ class SnapshotMetadata:
 # pickle an order of magnitude faster, and a receiver only rebuilds entries when somebody asks for them
 # (`SnapshotMetadata.lazy`): rank 0 in the thread that writes the metadata file, the others not at all unless
 # the snapshot object is used to restore.
-def encode_manifest(manifest: Manifest, tensor_columns: Optional[Any] = None, rest: Optional[Manifest] = None) -> bytes:
-    """`manifest` as bytes.  `tensor_columns` = (entries dict, pickled columns) from an earlier call with the SAME
+def encode_manifest(manifest: Manifest, tensor_columns: Optional[Any] = None, rest: Optional[Manifest] = None,
+                    parts: bool = False) -> Any:
+    """`manifest` as bytes (`parts`: as the two byte strings the wire form is the pickle of, for
+    `manifest_digest`).  `tensor_columns` = (entries dict, pickled columns) from an earlier call with the SAME
     TensorEntry objects (see `tensor_columns_of`) skips re-encoding them; they then come last in the decoded
     manifest.  `rest`, with `tensor_columns`, is the caller's statement that `manifest` is exactly `rest` plus
     the entries of `tensor_columns`: only `rest` is walked then."""
@@ -385,7 +387,18 @@ def encode_manifest(manifest: Manifest, tensor_columns: Optional[Any] = None, re
         else:
             others.append((len(paths), path, e))  # position among the tensor entries, to restore the order
     head = pickle.dumps((paths, locations, serializers, dtypes, shapes, replicated, ranges, others), protocol=5)
+    if parts:
+        return head, tensor_columns[1] if tensor_columns is not None else None
     return pickle.dumps((head, tensor_columns[1] if tensor_columns is not None else None), protocol=5)
+
+
+def manifest_digest(head: bytes, tensor_columns: Optional[Any]) -> bytes:
+    """16 + 16 bytes that change when the encoded manifest (`head`, plus the cached columns when there are any)
+    changes: the columns' digest was made once, with the columns."""
+    import hashlib
+
+    tail = tensor_columns[2] if tensor_columns is not None else b"\0" * 16
+    return hashlib.blake2b(head, digest_size=16).digest() + tail
 
 
 def tensor_columns_of(entries: Dict[str, Any]) -> Any:
@@ -396,7 +409,9 @@ def tensor_columns_of(entries: Dict[str, Any]) -> Any:
     blob = pickle.dumps((list(entries.keys()), [e.location for e in vals], [e.serializer for e in vals],
                          [e.dtype for e in vals], [e.shape for e in vals], [e.replicated for e in vals],
                          [e.byte_range for e in vals], []), protocol=5)
-    return (entries, blob)
+    import hashlib
+
+    return (entries, blob, hashlib.blake2b(blob, digest_size=16).digest())
 
 
 def _decode_columns(blob: bytes, out: Manifest) -> None:

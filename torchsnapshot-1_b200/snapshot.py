@@ -38,6 +38,7 @@ from .flatten import _encode, flatten, inflate
 from .io_preparer import _is_sharded_tensor, prepare_read, prepare_write
 from .io_types import ReadIO, ReadReq, StoragePlugin, WriteIO, WriteReq
 from .manifest import (
+    manifest_digest,
     Entry,
     Manifest,
     PrimitiveEntry,
@@ -713,22 +714,38 @@ class Snapshot:
                 last = next(reversed(object_entries))
                 if columns[0].get(last) is object_entries[last] and len(rest_of_manifest) + len(object_entries) == len(manifest):
                     rest = rest_of_manifest
-            parts: List[Any] = [None] * world
-            pg.all_gather_object(parts, (bool(replicated_paths), encode_manifest(manifest, columns, rest)), large=True)
+            # First a digest of what this rank would send, next to what it remembers of the previous exchange:
+            # when every rank's manifest is what it was last time (a job that checkpoints the same state again),
+            # the previous metadata document stands and no manifest travels.  Decided from gathered data only,
+            # so every rank decides alike; a rank that remembers nothing (its caches were cleared) makes all
+            # of them exchange the manifests.
+            import hashlib
+            import pickle
+
             global _last_gathered_manifests
-            if _last_gathered_manifests is not None and _last_gathered_manifests[0] == parts:
-                metadata = _last_gathered_manifests[1]  # every rank sent what it sent last time: same document
-            elif any(flag for flag, _blob in parts):
-                manifests = consolidate_replicated_entries([decode_manifest(blob) for _flag, blob in parts])
-                global_manifest: Manifest = {}
-                for r, m in enumerate(manifests):
-                    prefix = f"{r}/"
-                    for logical_path, entry in m.items():
-                        global_manifest[prefix + logical_path] = entry
-                metadata = SnapshotMetadata(version=VERSION, world_size=world, manifest=global_manifest)
+            head, tail = encode_manifest(manifest, columns, rest, parts=True)
+            mine = manifest_digest(head, columns)
+            remembered = _last_gathered_manifests[0] if _last_gathered_manifests is not None else None
+            said: List[Any] = [None] * world
+            pg.all_gather_object(said, (bool(replicated_paths), mine, remembered))
+            exchange = hashlib.blake2b(
+                b"".join((b"R" if flag else b"-") + digest for flag, digest, _r in said), digest_size=16).digest()
+            if all(r == exchange for _flag, _digest, r in said):
+                metadata = _last_gathered_manifests[1]  # every rank would send what it sent last time: same document
             else:
-                metadata = LazySnapshotMetadata(VERSION, world, [blob for _flag, blob in parts])
-            _last_gathered_manifests = (parts, metadata)
+                blobs: List[Any] = [None] * world
+                pg.all_gather_object(blobs, pickle.dumps((head, tail), protocol=5), large=True)
+                if any(flag for flag, _digest, _r in said):
+                    manifests = consolidate_replicated_entries([decode_manifest(blob) for blob in blobs])
+                    global_manifest: Manifest = {}
+                    for r, m in enumerate(manifests):
+                        prefix = f"{r}/"
+                        for logical_path, entry in m.items():
+                            global_manifest[prefix + logical_path] = entry
+                    metadata = SnapshotMetadata(version=VERSION, world_size=world, manifest=global_manifest)
+                else:
+                    metadata = LazySnapshotMetadata(VERSION, world, blobs)
+                _last_gathered_manifests = (exchange, metadata)
         mark("manifest_gather")
 
         pending = sync_execute_write_reqs(
