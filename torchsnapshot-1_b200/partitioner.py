@@ -198,12 +198,13 @@ class Negotiation:
 
 
 # The assignment of the previous take with the same loads: {"key", "out" (per rank: [(path, idx)]), "bytes" (per
-# rank), "speeds" (what the ranks reported then)}.  Kept while no rank's share of the box's throughput has moved by
-# more than 12 % since, so
-# that a job checkpointing the same state again and again writes the same files from the same ranks -- and every
-# rank can reuse its whole plan (snapshot.py) instead of planning a slightly different share each time.
+# rank), "speeds" (what the ranks reported then), "sizes", "loads", "judged_speeds"}.  Kept while a fresh split
+# for the throughputs reported now would not finish noticeably earlier (previous_assignment_stands), so that a
+# job checkpointing the same state again and again writes the same files from the same ranks -- and every rank
+# can reuse its whole plan (snapshot.py) instead of planning a slightly different share each time.
 _last_assignment: Optional[Dict[str, Any]] = None
-_STICKY_SLACK = 1.12
+_JUDGE_AGAIN_DRIFT = 0.03
+_REBALANCE_GAIN = 1.04
 
 
 def negotiate(pg: Any, non_replicated_size: int, loads_digest: str, agree_on: Optional[str],
@@ -221,24 +222,42 @@ def negotiate(pg: Any, non_replicated_size: int, loads_digest: str, agree_on: Op
 
 def previous_assignment_stands(neg: Negotiation) -> bool:
     """True when every rank still holds the previous plan for these loads and the previous assignment is still
-    good enough for the throughputs reported now (the same answer on every rank: gathered data only)."""
+    good enough for the throughputs reported now (the same answer on every rank: gathered data only).
+
+    "Good enough": while no rank's share of the box's throughput has moved by more than 3 % since the split was
+    last judged, it stands unjudged.  Otherwise the slowest rank's predicted time under the standing split is
+    compared with what a fresh split for today's throughputs would give: it stands unless the fresh one is more
+    than 4 % shorter (whatever the granularity of the loads allows: a split that cannot be improved is never
+    given up)."""
     if not neg.everybody_can_repeat or _last_assignment is None or _last_assignment["key"] != neg.key():
         return False
     speeds = [g[2] for g in neg.gathered]
     then = _last_assignment["speeds"]
     if not all(speeds) or not all(then):
         return all(speeds) == all(then)
-    # the split was made for the relative throughputs of that time: it stands while no rank's share of the
-    # box's throughput has moved by more than 12 % (whatever the granularity of the loads)
-    mean_now, mean_then = sum(speeds) / len(speeds), sum(then) / len(then)
-    return all(abs((a / mean_now) / (b / mean_then) - 1.0) <= _STICKY_SLACK - 1.0 for a, b in zip(speeds, then))
+    judged = _last_assignment.get("judged_speeds") or then
+    mean_now, mean_judged = sum(speeds) / len(speeds), sum(judged) / len(judged)
+    drift = max(abs((a / mean_now) / (b / mean_judged) - 1.0) for a, b in zip(speeds, judged))
+    if drift <= _JUDGE_AGAIN_DRIFT:
+        return True
+    nonrep = [g[0] for g in neg.gathered]
+    sizes = _last_assignment["sizes"]
+    standing = max((nonrep[r] + _last_assignment["bytes"][r]) / speeds[r] for r in range(len(speeds)))
+    fresh_out = assign_write_loads(_last_assignment["loads"], nonrep, speeds)
+    fresh = max((nonrep[r] + sum(sizes[u] for u in fresh_out[r])) / speeds[r] for r in range(len(speeds)))
+    if standing > fresh * _REBALANCE_GAIN:
+        return False
+    _last_assignment["judged_speeds"] = speeds
+    return True
 
 
-def _remember_assignment(neg: Negotiation, out: List[List[Tuple[str, int]]], sizes: Dict[Tuple[str, int], int]) -> None:
+def _remember_assignment(neg: Negotiation, out: List[List[Tuple[str, int]]], sizes: Dict[Tuple[str, int], int],
+                         loads: Optional[Sequence[Tuple[str, int, int, bool]]] = None) -> None:
     global _last_assignment
     _last_assignment = {"key": neg.key(), "digest": neg.gathered[0][1], "out": out,
                         "bytes": [sum(sizes[u] for u in mine) for mine in out],
-                        "speeds": [g[2] for g in neg.gathered]}
+                        "speeds": [g[2] for g in neg.gathered], "sizes": sizes,
+                        "loads": list(loads) if loads is not None else [(p, i, sz, False) for (p, i), sz in sizes.items()]}
 
 
 def probe_if_unseeded(any_device_stageable: bool) -> None:
@@ -307,7 +326,7 @@ def partition_write_reqs(
     speeds = [g[2] for g in gathered]
     out = assign_write_loads(base_loads, [g[0] for g in gathered], speeds if all(speeds) else None)
     if negotiated.same_loads:
-        _remember_assignment(negotiated, out, {(p, i): sz for p, i, sz, _sub in base_loads})
+        _remember_assignment(negotiated, out, {(p, i): sz for p, i, sz, _sub in base_loads}, base_loads)
     mine = sorted(out[rank])
     new_entries: Dict[str, Entry] = {k: v for k, v in entries.items() if k not in replicated}
     new_wrs: Dict[str, List[WriteReq]] = {k: v for k, v in write_reqs.items() if k not in replicated}

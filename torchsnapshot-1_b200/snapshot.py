@@ -202,7 +202,7 @@ class _RepeatTake:
     are not chunked (a DDP model plus tensor-valued optimizer state).  The next take may repeat the plan
     when (1) this rank's tensors are where and what they were (same paths, addresses, shapes, strides, dtypes:
     `TakePlanCache.fingerprint`), (2) every other rank says the same of its own, and (3) the previous split of the
-    writes still stands: no rank's share of the reported throughputs has moved by more than 12 % (partitioner.py) -- (2) and (3)
+    writes still stands: a fresh split for the throughputs reported now would not end noticeably earlier (partitioner.py) -- (2) and (3)
     are decided from the gathered exchange, identically on every rank.  Anything else plans afresh.
     TSB200_PLAN_CACHE=0 turns it off."""
 
