@@ -85,3 +85,32 @@ def test_ranks_without_a_measured_speed():
     P._remember_assignment(neg, out, {(p, i): sz for p, i, sz, _sub in loads}, loads)
     assert P.previous_assignment_stands(_negotiation([None, None]))
     assert not P.previous_assignment_stands(_negotiation([40.0, 41.0]))  # speeds have appeared: split by them
+
+
+def test_speed_estimate_is_the_median_of_the_last_takes():
+    saved, ctx = dict(P._speed_estimates), P.speed_context()
+    try:
+        P._speed_estimates.clear()
+        P.set_speed_context("SinkA")
+        assert P.observed_speed() is None
+        P._speed_estimates[""] = [30.0]  # the probed seed
+        assert P.observed_speed() == 30.0
+        P.record_take_speed(4 << 30, 100.0)  # 42.9 GB/s
+        assert abs(P.observed_speed() - (4 << 30) / 100.0 / 1e6) < 1e-9  # a measurement replaces the seed
+        for ms in (100.0, 101.0, 99.0):
+            P.record_take_speed(4 << 30, ms)
+        before = P.observed_speed()
+        P.record_take_speed(4 << 30, 160.0)  # one slow take
+        assert abs(P.observed_speed() - before) / before < 0.011
+        for ms in (160.0, 161.0, 159.0):  # the rank really is slower now: the estimate follows within three takes
+            P.record_take_speed(4 << 30, ms)
+        assert abs(P.observed_speed() - (4 << 30) / 160.0 / 1e6) / P.observed_speed() < 0.01
+        assert len(P._speed_estimates["SinkA"]) == P._SPEED_SAMPLES
+        P.record_take_speed(1 << 20, 1.0)  # too small to say anything
+        assert len(P._speed_estimates["SinkA"]) == P._SPEED_SAMPLES
+        P.set_speed_context("SinkB")  # another kind of sink starts from the seed again
+        assert P.observed_speed() == 30.0
+    finally:
+        P._speed_estimates.clear()
+        P._speed_estimates.update(saved)
+        P.set_speed_context(ctx)

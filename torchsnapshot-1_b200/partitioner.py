@@ -92,11 +92,21 @@ def assign_write_loads(
     return out
 
 
-# This rank's throughput on its previous takes, GB/s: an EMA per KIND OF SINK (the class name of the storage
-# plugin the take wrote to).  What bounds a rank differs with the sink -- its host link when the sink is
-# faster than the link, the sink's own write path otherwise -- and so does the best split.
-_speed_estimates: Dict[str, float] = {}
+# This rank's throughput on its previous takes, GB/s: the last few measurements per KIND OF SINK (the class name
+# of the storage plugin the take wrote to); the estimate is their median, so that one slow take (another job on
+# the shared uplink, a page-cache hiccup) does not move the next split -- an EMA did: one 126 ms take among 78 ms
+# ones cost the rank an eighth of its share for the next three takes.  What bounds a rank differs with the sink
+# -- its host link when the sink is faster than the link, the sink's own write path otherwise -- and so does
+# the best split.  Key "" holds the probed seed.
+_SPEED_SAMPLES = 5
+_speed_estimates: Dict[str, List[float]] = {}
 _speed_context: str = ""
+
+
+def _median(samples: Sequence[float]) -> float:
+    ordered = sorted(samples)
+    mid = len(ordered) // 2
+    return ordered[mid] if len(ordered) % 2 else 0.5 * (ordered[mid - 1] + ordered[mid])
 
 
 def set_speed_context(kind: str) -> None:
@@ -112,8 +122,8 @@ def speed_context() -> str:
 def observed_speed() -> Optional[float]:
     """This rank's throughput as measured on its previous takes into this kind of sink; before the first,
     the probed device->host rate (None if that could not be measured either)."""
-    got = _speed_estimates.get(_speed_context)
-    return got if got is not None else _speed_estimates.get("")
+    got = _speed_estimates.get(_speed_context) or _speed_estimates.get("")
+    return _median(got) if got else None
 
 
 def probe_speed(device: Optional[int] = None, nbytes: int = 256 << 20) -> Optional[float]:
@@ -160,8 +170,9 @@ def record_take_speed(nbytes: int, ms: float, kind: Optional[str] = None) -> Non
         return  # too small to say anything
     kind = _speed_context if kind is None else kind
     gbps = nbytes / ms / 1e6
-    prev = _speed_estimates.get(kind)
-    _speed_estimates[kind] = gbps if prev is None else 0.65 * prev + 0.35 * gbps
+    samples = _speed_estimates.setdefault(kind, [])
+    samples.append(gbps)
+    del samples[:-_SPEED_SAMPLES]
 
 
 class RanksDisagree(RuntimeError):
@@ -266,7 +277,7 @@ def probe_if_unseeded(any_device_stageable: bool) -> None:
     if any_device_stageable and observed_speed() is None:
         seed = probe_speed()
         if seed:
-            _speed_estimates[""] = seed
+            _speed_estimates[""] = [seed]
 
 
 def partition_write_reqs(
