@@ -50,3 +50,19 @@ def test_empty_containers_and_scalars():
     assert inflate(manifest, flat, "k") == {"e": {}, "l": [], "x": None}
     manifest, flat = flatten(5, "k")
     assert manifest == {} and flat == {"k": 5}
+
+
+def test_wide_dicts_get_their_paths_back_and_follow_changes():
+    d = {f"w{i}": i for i in range(3000)}
+    _m, first = flatten(d, "big")
+    _m, again = flatten(d, "big")
+    assert list(again) == list(first) and all(a is b for a, b in zip(again, first))  # the same string objects
+    again.pop("big/w0")  # the caller's dict is its own
+    assert "big/w0" in flatten(d, "big")[1]
+    d["extra/1"] = -1
+    del d["w5"]
+    _m, changed = flatten(d, "big")
+    assert "big/w5" not in changed and changed["big/extra%2F1"] == -1 and len(changed) == 3000
+    assert list(changed)[:3] == ["big/w0", "big/w1", "big/w2"]
+    _m, other = flatten({f"v{i}": i for i in range(3000)}, "big")  # another dict under the same prefix
+    assert list(other)[0] == "big/v0"

@@ -36,6 +36,29 @@ def _flattenable_dict(d: Dict[Any, Any]) -> bool:
 
 _CONTAINER_TYPES = frozenset((list, dict, OrderedDict))
 
+# Child paths of the wide dicts flattened last (container path -> (keys, child paths)): a job that checkpoints the
+# same state dict again gets the same 10-20 k path strings back instead of formatting them again (and everything
+# downstream that compares or hashes paths meets the same objects).  A handful of entries, replaced as they come.
+_WIDE = 1024
+_wide_paths: Dict[str, Tuple[Any, Any]] = {}
+
+
+def _child_paths(path: str, keys: Any) -> Any:
+    wide = len(keys) >= _WIDE
+    if wide:
+        hit = _wide_paths.get(path)
+        if hit is not None and hit[0] == keys:
+            return hit[1]
+    if set(map(type, keys)) == _STR_ONLY and "%" not in (joined := "".join(keys)) and "/" not in joined:
+        out = [f"{path}/{k}" for k in keys]
+    else:
+        out = [f"{path}/{_encode(str(k))}" for k in keys]
+    if wide:
+        if len(_wide_paths) >= 8 and path not in _wide_paths:
+            _wide_paths.pop(next(iter(_wide_paths)))
+        _wide_paths[path] = (list(keys), out)
+    return out
+
 
 def flatten(obj: Any, prefix: str) -> Tuple[Manifest, Dict[str, Any]]:
     manifest: Manifest = {}
@@ -54,10 +77,7 @@ def flatten(obj: Any, prefix: str) -> Tuple[Manifest, Dict[str, Any]]:
             if len(keys) > 8 and _CONTAINER_TYPES.isdisjoint(map(type, node.values())):
                 # a dict of leaves (a model's state dict, the bulk of a 20 k-tensor checkpoint): its leaves are
                 # next in pre-order whatever is still waiting on the stack, so they go in as they are
-                if set(map(type, keys)) == _STR_ONLY and "%" not in (joined := "".join(keys)) and "/" not in joined:
-                    flattened.update(zip([f"{path}/{k}" for k in keys], node.values()))
-                else:
-                    flattened.update(zip([f"{path}/{_encode(str(k))}" for k in keys], node.values()))
+                flattened.update(zip(_child_paths(path, keys), node.values()))
                 continue
             stack.extend((node[k], f"{path}/{_encode(str(k))}") for k in reversed(keys))
         else:
