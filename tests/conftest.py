@@ -10,6 +10,21 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 
 import tsb200_loader  # noqa: E402
 
+
+def _build_missing_native_pieces():
+    """The in-tree libraries are build products (git-ignored): when a checkout has none yet -- the suite was
+    started before __graft_entry__.build() -- make them here, before the package is imported.  On the GPU box
+    they travel with the snapshot and nothing is built."""
+    import shutil
+    import subprocess
+
+    csrc = os.path.join(ROOT, "torchsnapshot-1_b200", "csrc")
+    missing = [t for t in ("libtsb200.so", "_tsb200_meta.so") if not os.path.exists(os.path.join(csrc, t))]
+    if missing and shutil.which("make") and (shutil.which("nvcc") or os.path.exists("/usr/local/cuda/bin/nvcc")):
+        subprocess.run(["make", "-C", csrc] + missing, check=False, capture_output=True)
+
+
+_build_missing_native_pieces()
 tsb200_loader.load()
 
 
