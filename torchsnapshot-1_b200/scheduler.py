@@ -77,6 +77,7 @@ def read_concurrency() -> int:
     return min(io_concurrency(), 6)
 
 
+_LARGE_FILE_BYTES = 256 << 20  # files from here on count half in a streaming batch (drain_wave)
 _TRACE_READS = os.environ.get("TSB200_TRACE_READS") == "1"
 _TRACE_WRITES = os.environ.get("TSB200_TRACE_WRITES") == "1"
 # streamed writes: files of a batch cross the link interleaved in chunks of this size and are written as they
@@ -376,7 +377,7 @@ async def execute_write_reqs(
         pass
     tasks: Set["asyncio.Future[Any]"] = set()
     io_slots = asyncio.Semaphore(io_concurrency())
-    stream_batch = max(io_concurrency() // 2, 1)  # files interleaved on the link: half of the writers, so that the
+    stream_batch = int(os.environ.get("TSB200_STREAM_BATCH", 0)) or max(io_concurrency() // 2, 1)  # files interleaved on the link: half of the writers, so that the
     # next batch's first chunks find free writers while this batch's last ones are still being written
     alloc = _Allocator(memory_budget_bytes)
 
@@ -495,10 +496,19 @@ async def execute_write_reqs(
                     del pbuf
                     i += 1
                     continue
-                # a batch: as many files as there are writers, or as pinned memory holds right now
+                # a batch: half as many slab-sized files as there are writers (the next batch's first chunks then
+                # find free writers), up to as many LARGE files as there are writers -- a large file keeps its one
+                # writer busy for 150 ms and more, and files that start late end late (20 x 400 MiB: 26 GB/s in
+                # batches of 16 + 4, 31.5 GB/s in one batch; the slab workload loses 10 % with batches of 24-32:
+                # profiles/r02_stream_batch_sweep.txt) -- or as pinned memory holds right now
                 batch: List[Tuple[str, int, int, PinnedBuffer]] = []
-                while i < len(files) and len(batch) < stream_batch:
+                room = 2 * stream_batch
+                while i < len(files):
                     path, off, nbytes = files[i]
+                    cost = 1 if nbytes >= _LARGE_FILE_BYTES else 2
+                    if batch and cost > room:
+                        break
+                    room -= cost
                     if not batch:
                         pbuf = await alloc.pinned(eng, nbytes)
                     else:
