@@ -516,12 +516,12 @@ def main():
         os.makedirs(root, exist_ok=True)
         barrier()
 
-        def run(write):
+        def run(write, tag):
             errs = []
 
             def one(i):
                 try:
-                    p = os.path.join(root, f"r{rank}_{i}")
+                    p = os.path.join(root, f"r{rank}_{i}_{tag}")
                     if write:
                         _native.file_write(p, h + i * M, M, 1)
                     else:
@@ -540,8 +540,14 @@ def main():
             assert not errs, errs
             return world * files * M / dt / 1e9
 
-        w = run(True)
-        r = run(False)
+        # best of three passes each (a single 0.1 s pass ranged from 29 to 43 GB/s from run to run); every write
+        # pass makes new files, like a take does, and every read pass reads files that have not been read yet,
+        # like a restore does (reading the same files again runs 10-25 % faster and is not what a restore sees)
+        fs_stat = os.statvfs(root)
+        free = -max_over_ranks(-float(fs_stat.f_bavail * fs_stat.f_frsize))  # the same answer on every rank
+        passes = 3 if free > (48 << 30) else 1  # 3 x 4 GiB of files for a moment
+        w = max(run(True, k) for k in range(passes))
+        r = max(run(False, k) for k in range(passes))
         barrier()
         if rank == 0:
             shutil.rmtree(root, ignore_errors=True)
@@ -555,7 +561,7 @@ def main():
                 "tmpfs_write_gbps": round(w, 1), "tmpfs_read_gbps": round(r, 1), "host_cores": os.cpu_count(),
                 "how": (f"1 GiB pinned<->device x4 on every rank at once (CUDA events); {world * files} files of 128 MiB "
                         "written then read by one thread each from / into memory of its own, all ranks at once "
-                        "(wall clock, max over ranks)")}
+                        "(wall clock, max over ranks, best of 3 passes over files of their own)")}
 
     ceilings = measure_ceilings()
     log("[bench] ceilings", json.dumps(ceilings))
