@@ -509,7 +509,7 @@ def main():
         # source / destination memory of its own (writers that share a 1 GiB source read it out of the last-level
         # cache and overstate the ceiling: 55 GB/s against 39 GB/s for a take whose D2H had long finished)
         M = 128 << 20
-        files = max(32 // world, 2)
+        files = max(4, min(32, 2 * (os.cpu_count() or 8) // world))  # the writers a rank keeps busy (scheduler.io_concurrency)
         ctx.host_free(h)
         h = ctx.host_alloc(files * M)
         root = os.path.join(base, "ceil")
@@ -545,7 +545,7 @@ def main():
         # like a restore does (reading the same files again runs 10-25 % faster and is not what a restore sees)
         fs_stat = os.statvfs(root)
         free = -max_over_ranks(-float(fs_stat.f_bavail * fs_stat.f_frsize))  # the same answer on every rank
-        passes = 3 if free > (48 << 30) else 1  # 3 x 4 GiB of files for a moment
+        passes = 3 if free > (64 << 30) else 1  # 3 x (4 to 8 GiB) of files for a moment
         w = max(run(True, k) for k in range(passes))
         r = max(run(False, k) for k in range(passes))
         barrier()
