@@ -520,3 +520,86 @@ def test_take_plan_cache_hits_only_on_identical_tensors():
     retyped[7] = retyped[7].view(torch.int32)
     assert cache.get(cfg, paths, retyped) is None
     assert cache.get(cfg, paths, again) is not None
+
+
+def test_bulk_read_planner_keeps_devices_apart():
+    """Members of one slab file bound for two devices never share a read (one consumer = one device's staging
+    block and one launch): the device column of the table joins the sort key of plan_cuda_read_columns."""
+    import numpy as np
+
+    from torchsnapshot_b200 import tensor_table as tt
+    from torchsnapshot_b200.batcher import plan_cuda_read_columns
+
+    tensors = [torch.zeros(100, 2) for _ in range(40)]
+    table = tt.scan(tensors).copy()
+    table[:, tt.DEVICE] = np.arange(40) % 2  # pretend: even members on device 0, odd ones on device 1
+    lo = np.arange(40, dtype=np.int64) * 800
+    hi = lo + 800
+    file_id = np.zeros(40, dtype=np.int64)
+    reads = plan_cuda_read_columns(["batched/f"], file_id, lo, hi, tensors, table)
+    assert len(reads) == 2 and sorted(rr.buffer_consumer.device for rr in reads) == [0, 1]
+    for rr in reads:
+        dev = rr.buffer_consumer.device
+        members = [i for i in range(40) if i % 2 == dev]
+        assert rr.byte_range == (int(lo[members[0]]), int(hi[members[-1]]))
+        assert [t is tensors[i] for t, i in zip(rr.buffer_consumer.tensors, members)] == [True] * 20
+        assert (rr.buffer_consumer._offsets == lo[members] - lo[members[0]]).all()
+
+
+def test_restore_view_splits_a_manifest_into_columns_and_the_rest():
+    """snapshot._RestoreView: slab members of buffer-protocol dtypes under the prefix become columns, containers
+    are kept apart, everything else (whole-file tensors, pickled tensors, objects, sharded and chunked entries,
+    other statefuls) is left to the per-entry planner."""
+    from torchsnapshot_b200 import tensor_table as tt
+    from torchsnapshot_b200.manifest import (ChunkedTensorEntry, DictEntry, ObjectEntry, PrimitiveEntry, Shard,
+                                             ShardedTensorEntry)
+    from torchsnapshot_b200.snapshot import _RestoreView
+
+    def tensor(location, dtype, shape, byte_range, serializer="buffer_protocol", replicated=False):
+        return TensorEntry(location=location, serializer=serializer, dtype=dtype, shape=shape, replicated=replicated,
+                           byte_range=byte_range)
+
+    manifest = {
+        "m": DictEntry(keys=["a", "b", "c", "d", "e", "f", "g", "h"]),
+        "m/a": tensor("batched/x", "torch.float32", [3, 4], [0, 48]),
+        "m/b": tensor("batched/x", "torch.bfloat16", [], [48, 50], replicated=True),
+        "m/c": tensor("0/m/c", "torch.float32", [1000, 1000], None),  # a file of its own
+        "m/d": tensor("batched/y", "torch.complex64", [2], [0, 99], serializer="torch_save"),
+        "m/e": ObjectEntry(location="0/m/e", serializer="torch_save", obj_type="tuple", replicated=False),
+        "m/f": PrimitiveEntry.from_object(5),
+        "m/g": ShardedTensorEntry(shards=[Shard(offsets=[0], sizes=[4], tensor=tensor("sharded/g_0", "torch.int64", [4], [50, 82]))]),
+        "m/h": ChunkedTensorEntry(dtype="torch.float32", shape=[8], chunks=[], replicated=False),
+        "m/i": tensor("batched/y", "torch.int64", [2, 2, 2, 2, 2, 2, 2, 2, 2], [100, 4196]),  # 9 dims: not a row of the table
+        "other": DictEntry(keys=["a"]),
+        "other/a": tensor("batched/x", "torch.float32", [1], [82, 86]),
+        "mm/a": tensor("batched/x", "torch.float32", [1], [86, 90]),  # "mm" is not under "m"
+    }
+    view = _RestoreView(manifest, {}, "m")
+    assert view.paths == ["m/a", "m/b"] and [e is manifest[p] for e, p in zip(view.entries, view.paths)] == [True, True]
+    assert list(view.containers) == ["m"] and view.has_sharded
+    assert [p for p, _e in view.rest] == ["m/c", "m/d", "m/e", "m/f", "m/g", "m/h", "m/i"]
+    assert view.dtype_codes.tolist() == [tt.dtype_code(torch.float32), tt.dtype_code(torch.bfloat16)]
+    assert view.ndims.tolist() == [2, 0] and view.shapes[0, :3].tolist() == [3, 4, 0] and not view.shapes[1].any()
+    assert view.los.tolist() == [0, 48] and view.his.tolist() == [48, 50]
+    assert view.locations == ["batched/x"] and view.file_ids.tolist() == [0, 0] and view.replicated.tolist() == [False, True]
+    other = _RestoreView(manifest, {}, "other")
+    assert other.paths == ["other/a"] and not other.has_sharded and not other.rest
+    empty = _RestoreView(manifest, {}, "absent")
+    assert empty.paths == [] and empty.shapes.shape == (0, tt.MAX_DIMS) and empty.los.shape == (0,)
+
+
+def test_streaming_batches_count_large_files_half():
+    """scheduler.streaming_batch_len: 16 slab-sized files per interleaved batch with 32 writers, up to 32 files
+    of 256 MiB and more, mixtures in between; never an empty batch."""
+    from torchsnapshot_b200.scheduler import streaming_batch_len
+
+    slab, big = 128 << 20, 400 << 20
+    assert streaming_batch_len([slab] * 60, 16) == 16
+    assert streaming_batch_len([big] * 20, 16) == 20
+    assert streaming_batch_len([big] * 40, 16) == 32
+    assert streaming_batch_len([big] * 3 + [slab] * 60, 16) == 3 + 14  # 3 + 2 * 14 = 31 of 32
+    assert streaming_batch_len([slab] * 5, 16) == 5
+    assert streaming_batch_len([slab], 1) == 1 and streaming_batch_len([slab, slab], 1) == 1
+    assert streaming_batch_len([big, slab], 1) == 1 and streaming_batch_len([big, big, big], 1) == 2
+    assert streaming_batch_len([], 16) == 0
+    assert streaming_batch_len([256 << 20] * 40, 8) == 16 and streaming_batch_len([(256 << 20) - 1] * 40, 8) == 8

@@ -66,6 +66,19 @@ def io_concurrency() -> int:
     return max(4, min(_MAX_PER_RANK_IO_CONCURRENCY, 2 * cores // _local_world_size))
 
 
+def streaming_batch_len(sizes: List[int], stream_batch: int) -> int:
+    """How many of the files whose sizes are given (in order) form the next interleaved batch of a streamed take:
+    `stream_batch` slab-sized files, large files counting half (see drain_wave); at least one."""
+    room, n = 2 * stream_batch, 0
+    for nbytes in sizes:
+        cost = 1 if nbytes >= _LARGE_FILE_BYTES else 2
+        if n and cost > room:
+            break
+        room -= cost
+        n += 1
+    return max(n, 1) if sizes else 0
+
+
 def read_concurrency() -> int:
     """Storage READS in flight for this rank.  A read's bytes are useless to the device until the whole
     request is in pinned memory, so the read side wants few requests in flight with several pread workers
@@ -502,13 +515,9 @@ async def execute_write_reqs(
                 # batches of 16 + 4, 31.5 GB/s in one batch; the slab workload loses 10 % with batches of 24-32:
                 # profiles/r02_stream_batch_sweep.txt) -- or as pinned memory holds right now
                 batch: List[Tuple[str, int, int, PinnedBuffer]] = []
-                room = 2 * stream_batch
-                while i < len(files):
+                stop = i + streaming_batch_len([f[2] for f in files[i:i + 2 * stream_batch]], stream_batch)
+                while i < stop:
                     path, off, nbytes = files[i]
-                    cost = 1 if nbytes >= _LARGE_FILE_BYTES else 2
-                    if batch and cost > room:
-                        break
-                    room -= cost
                     if not batch:
                         pbuf = await alloc.pinned(eng, nbytes)
                     else:
