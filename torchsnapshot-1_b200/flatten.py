@@ -55,7 +55,10 @@ def _child_paths(path: str, keys: Any) -> Any:
         out = [f"{path}/{_encode(str(k))}" for k in keys]
     if wide:
         if len(_wide_paths) >= 8 and path not in _wide_paths:
-            _wide_paths.pop(next(iter(_wide_paths)))
+            try:
+                _wide_paths.pop(next(iter(_wide_paths)), None)
+            except (StopIteration, RuntimeError):  # another thread emptied or resized it meanwhile
+                pass
         _wide_paths[path] = (list(keys), out)
     return out
 
