@@ -66,3 +66,67 @@ def test_wide_dicts_get_their_paths_back_and_follow_changes():
     assert list(changed)[:3] == ["big/w0", "big/w1", "big/w2"]
     _m, other = flatten({f"v{i}": i for i in range(3000)}, "big")  # another dict under the same prefix
     assert list(other)[0] == "big/v0"
+
+
+def _reference_walk(obj, path, manifest, flat):
+    """The grammar restated recursively (reference flatten.py:18-120): containers first, children in order."""
+    if type(obj) is list:
+        manifest[path] = "list"
+        for i, v in enumerate(obj):
+            _reference_walk(v, f"{path}/{i}", manifest, flat)
+    elif type(obj) in (dict, OrderedDict) and all(isinstance(k, (str, int)) for k in obj) \
+            and len({str(k) for k in obj}) == len(obj):
+        manifest[path] = ("OrderedDict" if type(obj) is OrderedDict else "dict", list(obj.keys()))
+        for k, v in obj.items():
+            enc = str(k).replace("%", "%25").replace("/", "%2F")
+            _reference_walk(v, f"{path}/{enc}", manifest, flat)
+    else:
+        flat[path] = obj
+
+
+def test_random_trees_against_the_recursive_restatement():
+    import random
+
+    rnd = random.Random(20)
+
+    def key():
+        kind = rnd.random()
+        if kind < 0.15:
+            return rnd.randrange(50)
+        alphabet = "abc/%._0"
+        return "".join(rnd.choice(alphabet) for _ in range(rnd.randrange(1, 6)))
+
+    def tree(depth):
+        kind = rnd.random()
+        if depth == 0 or kind < 0.35:
+            return rnd.choice([1, 2.5, "s", None, (1, 2), torch.zeros(1)])
+        if kind < 0.55:
+            return [tree(depth - 1) for _ in range(rnd.randrange(0, 4))]
+        n = rnd.choice([0, 1, 3, 12, 40])
+        d = OrderedDict() if rnd.random() < 0.3 else {}
+        for _ in range(n):
+            d[key()] = tree(depth - 1) if rnd.random() < 0.4 else rnd.randrange(100)
+        return d
+
+    for _ in range(300):
+        obj = tree(4)
+        prefix = rnd.choice(["k", "a/b", "p%q"])
+        manifest, flat = flatten(obj, prefix)
+        want_m, want_f = {}, {}
+        _reference_walk(obj, prefix.replace("%", "%25").replace("/", "%2F"), want_m, want_f)
+        assert list(flat) == list(want_f) and all(flat[p] is want_f[p] for p in flat)
+        assert list(manifest) == list(want_m)
+        for p, e in manifest.items():
+            assert (e.type == "list") if want_m[p] == "list" else (e.type, e.keys) == want_m[p]
+        back = inflate(manifest, flat, prefix)
+
+        def same(a, b):
+            if type(a) is not type(b):
+                return False
+            if isinstance(a, dict):
+                return list(a) == list(b) and all(same(a[k], b[k]) for k in a)
+            if isinstance(a, list):
+                return len(a) == len(b) and all(same(x, y) for x, y in zip(a, b))
+            return a is b or a == b
+
+        assert same(back, obj)
