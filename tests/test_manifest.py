@@ -59,3 +59,80 @@ def test_legacy_yaml_metadata_still_loads():
     text = "version: 0.0.1\nworld_size: 1\nmanifest:\n  0/foo:\n    type: Tensor\n    location: 0/foo\n    serializer: buffer_protocol\n    dtype: torch.float32\n    shape: [2, 3]\n    replicated: false\n    byte_range: null\n"
     md = SnapshotMetadata.from_yaml(text)
     assert md.manifest["0/foo"].shape == [2, 3] and md.manifest["0/foo"].byte_range is None
+
+
+# ---- the wire form of a rank's manifest (take-side exchange) ------------------------------------------------
+def _wire_manifest():
+    t = TensorEntry("batched/u1", "buffer_protocol", "torch.float32", [3, 4], False, [0, 48])
+    return {
+        "m": DictEntry(keys=["a", "b", 3]),
+        "m/a": t,
+        "m/b": TensorEntry("0/m/b", "buffer_protocol", "torch.bfloat16", [], True, None),
+        "m/3": PrimitiveEntry.from_object(2.5),
+        "m/l": ListEntry(),
+        "m/o": ObjectEntry(location="0/m/o", serializer="torch_save", obj_type="tuple", replicated=False),
+        "m/s": ShardedTensorEntry(shards=[Shard([0], [4], TensorEntry("sharded/s_0", "buffer_protocol", "torch.int64", [4], False, [48, 80]))]),
+        "m/c": ChunkedTensorEntry(dtype="torch.float32", shape=[8], chunks=[Shard([0], [8], t)], replicated=True),
+        "m/z": TensorEntry("batched/u1", "buffer_protocol", "torch.int8", [5], False, [80, 85]),
+    }
+
+
+def _as_objs(manifest):
+    return [(p, e.to_obj()) for p, e in manifest.items()]
+
+
+def test_encoded_manifest_decodes_to_the_same_entries_in_the_same_order():
+    from torchsnapshot_b200.manifest import LazySnapshotMetadata, decode_manifest, encode_manifest
+
+    manifest = _wire_manifest()
+    blob = encode_manifest(manifest)
+    assert isinstance(blob, bytes)
+    assert _as_objs(decode_manifest(blob)) == _as_objs(manifest)
+    assert _as_objs(decode_manifest(encode_manifest({}))) == []
+    lazy = LazySnapshotMetadata("0.0.3", 2, [blob, manifest])
+    assert "manifest" not in lazy.__dict__
+    want = [("0/" + p, o) for p, o in _as_objs(manifest)] + [("1/" + p, o) for p, o in _as_objs(manifest)]
+    assert _as_objs(lazy.manifest) == want and "manifest" in lazy.__dict__
+    assert SnapshotMetadata.from_yaml(lazy.to_yaml()).to_yaml() == lazy.to_yaml()
+
+
+def test_cached_columns_rest_and_digests():
+    """The tensor entries of a cached plan travel as columns encoded once (`tensor_columns_of`); with `rest` only
+    the other entries are walked; `manifest_digest` says whether the bytes a rank would send have changed."""
+    import pickle
+
+    from torchsnapshot_b200.manifest import decode_manifest, encode_manifest, manifest_digest, tensor_columns_of
+
+    manifest = _wire_manifest()
+    cached = {p: e for p, e in manifest.items() if type(e) is TensorEntry}
+    rest = {p: e for p, e in manifest.items() if p not in cached}
+    columns = tensor_columns_of(cached)
+    assert columns[0] is cached and len(columns[2]) == 16
+    plain = decode_manifest(encode_manifest(manifest))
+    for blob in (encode_manifest(manifest, columns), encode_manifest(manifest, columns, rest)):
+        got = decode_manifest(blob)
+        assert sorted(_as_objs(got)) == sorted(_as_objs(plain))  # cached entries come last, nothing is lost
+        assert list(got)[-len(cached):] == list(cached)
+    head, tail = encode_manifest(manifest, columns, rest, parts=True)
+    assert tail is columns[1] and pickle.dumps((head, tail), protocol=5) == encode_manifest(manifest, columns, rest)
+    # a `rest` that does not add up to the manifest is refused, not silently mis-encoded
+    try:
+        encode_manifest(manifest, columns, {"m": manifest["m"]})
+    except AssertionError:
+        pass
+    else:
+        raise AssertionError("encode_manifest accepted a `rest` that leaves entries out")
+    # digests: stable for the same content, different when a primitive, a location or the cached columns change
+    d0 = manifest_digest(head, columns)
+    assert len(d0) == 32 and d0 == manifest_digest(encode_manifest(manifest, columns, rest, parts=True)[0], columns)
+    changed = dict(rest)
+    changed["m/3"] = PrimitiveEntry.from_object(3.5)
+    head2, _ = encode_manifest({**changed, **cached}, columns, changed, parts=True)
+    assert manifest_digest(head2, columns) != d0
+    moved = {p: (TensorEntry("batched/u2", e.serializer, e.dtype, e.shape, e.replicated, e.byte_range) if e.location == "batched/u1" else e)
+             for p, e in cached.items()}
+    columns2 = tensor_columns_of(moved)
+    head3, _ = encode_manifest({**rest, **moved}, columns2, rest, parts=True)
+    assert head3 == head and manifest_digest(head3, columns2) != d0
+    head4, tail4 = encode_manifest(manifest, None, None, parts=True)
+    assert tail4 is None and manifest_digest(head4, None) != d0
